@@ -1,0 +1,264 @@
+/*
+ * gpuaudio.h — C ABI of libgpuaudio.so: the B200 (sm_100a) relay-audio ingest path
+ * that sits behind loqa-hub's Go audio handler (cgo package internal/gpuaudio).
+ *
+ * Plain C: pointers, sizes and PODs only — no CUDA, torch or C++ types.  Every
+ * entry point names the reference code it replaces (paths relative to the
+ * loqa-hub tree; see SURVEY.md §8a/§8b and INTEGRATION.md for the cgo binding).
+ *
+ * Conventions
+ *   - int return: 0 = GA_OK, negative = ga_status error class.  Never aborts,
+ *     never calls back into the caller.  ga_last_error() returns a thread-local,
+ *     NUL-terminated description of the last failure on the calling thread.
+ *   - There is NO CPU fallback: without a usable CUDA device every compute entry
+ *     point fails with GA_ERR_CUDA.
+ *   - "device pointer" arguments (ga_k_* layer) are CUDA device addresses owned by
+ *     the caller; `stream` is a cudaStream_t passed as void* (NULL = default stream).
+ *   - All structs are little-endian PODs with the exact layouts below (checked by
+ *     ga_abi_sizes()).
+ */
+#ifndef GPUAUDIO_H
+#define GPUAUDIO_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GA_ABI_VERSION 1
+
+typedef enum ga_status {
+    GA_OK            =  0,
+    GA_ERR_ARG       = -1,  /* bad argument (NULL, misaligned, out of range)     */
+    GA_ERR_CUDA      = -2,  /* CUDA runtime / driver error, or no device          */
+    GA_ERR_NOMEM     = -3,  /* host or device allocation failed                   */
+    GA_ERR_RING_FULL = -4,  /* pinned ring has no room until tickets are waited   */
+    GA_ERR_OVERFLOW  = -5,  /* a stream's sample arena / a batch limit overflowed */
+    GA_ERR_STATE     = -6,  /* call not valid in the current state (bad ticket …) */
+    GA_ERR_COMM      = -7   /* NCCL / multi-GPU exchange failure                  */
+} ga_status;
+
+/* RelayStatus — internal/grpc/audio_service.go:56-63 (same numeric values). */
+enum {
+    GA_RELAY_CONNECTED  = 0,
+    GA_RELAY_CONTENDING = 1,
+    GA_RELAY_WINNER     = 2,
+    GA_RELAY_CANCELLED  = 3
+};
+
+/* ga_msg.flags / ga_desc.flags — AudioChunk.IsWakeWord / IsEndOfSpeech
+ * (call sites audio_service.go:962, :1008) plus stream bookkeeping. */
+#define GA_MSG_WAKE   0x01u   /* chunk.IsWakeWord                                    */
+#define GA_MSG_EOS    0x02u   /* chunk.IsEndOfSpeech                                 */
+#define GA_MSG_FIRST  0x04u   /* first chunk of an utterance: resets the stream state */
+
+/* ga_k_ingest / ga_config mode bits: which parts of the path run. */
+#define GA_DO_CONVERT   0x01u /* int16 -> f32 samples materialised (bytesToFloat32Array) */
+#define GA_DO_FEATURES  0x02u /* per-message (+ optional per-frame) energy statistics    */
+#define GA_DO_SHA256    0x04u /* per-message SHA-256 fingerprint of the received bytes   */
+#define GA_DO_ALL       0x07u
+
+#define GA_FRAME_SAMPLES 320u /* 20 ms at 16 kHz                  */
+
+/* Per-message result record, 64 bytes.  The feature half is what the reference
+ * logs per conversion / per RMS calculation (audio_service.go:1093-1098, :843-849). */
+typedef struct ga_result {
+    uint8_t  digest[32];  /* SHA-256 of the message bytes exactly as received      */
+    double   sumsq;       /* "sum":  Σ float64(float32(s*s)) in index order (:824-828) */
+    double   rms;         /* "rms":  sqrt(sumsq / n_samples), 0 when n_samples == 0 (:841, :819-822) */
+    uint32_t n_samples;   /* "output_samples" = nbytes / 2 (:1066)                  */
+    uint32_t nonzero;     /* "non_zero_samples" (:1081-1083, :829-831)              */
+    float    peak;        /* "max_abs_value" / "max_sample" (:1084-1090, :832-838)  */
+    uint32_t flags;       /* bit 0: VAD (rms > vad_threshold); bits 8..: echo of ga_desc.flags */
+} ga_result;
+
+/* Per-frame record (20 ms framing, new spec — no reference counterpart), 32 bytes. */
+typedef struct ga_frame {
+    double   sumsq;
+    double   rms;
+    uint32_t n_samples;
+    uint32_t nonzero;
+    float    peak;
+    uint32_t vad;
+} ga_frame;
+
+/* Device-side message descriptor, 32 bytes (ga_k_* layer). */
+typedef struct ga_desc {
+    uint64_t in_off;     /* byte offset of the message in the PCM slab; multiple of 16     */
+    uint64_t out_off;    /* index of the message's first output sample in the f32 arena    */
+    uint32_t nbytes;     /* message length in bytes, any value (odd trailing byte dropped
+                            for conversion, kept for the digest)                           */
+    uint32_t stream_id;  /* dense stream slot                                              */
+    uint32_t flags;      /* GA_MSG_*                                                       */
+    uint32_t frame_off;  /* index of the message's first ga_frame (when frames are wanted)  */
+} ga_desc;
+
+/* ===================================================================== kernels
+ * Device-pointer layer: one call = one launch on `stream`, asynchronous.       */
+
+/* Fused relay-message ingest.  For every message i < n_msgs:
+ *   GA_DO_CONVERT : samples[desc[i].out_off + k] = float32(int16le(pcm, k)) / 32767.0f
+ *                   — replaces bytesToFloat32Array, audio_service.go:1048-1101
+ *   GA_DO_FEATURES: results[i].{sumsq,rms,n_samples,nonzero,peak,flags}; with
+ *                   frames != NULL also one ga_frame per GA_FRAME_SAMPLES samples
+ *                   — the statistics of calculateSignalStrength, audio_service.go:818-852,
+ *                   applied per message / per 20 ms frame, in the reference's order
+ *   GA_DO_SHA256  : results[i].digest = SHA-256(message bytes)
+ *                   — the voice-event audio fingerprint (README.md:50, API.md:170; hook
+ *                   events/voice_event.go:84-88)
+ * d_pcm must be readable up to the next multiple of 16 past every message end.
+ * d_samples may be NULL without GA_DO_CONVERT; d_frames may be NULL. */
+int ga_k_ingest(const void *d_pcm, const ga_desc *d_desc, uint32_t n_msgs,
+                float *d_samples, ga_result *d_results, ga_frame *d_frames,
+                uint32_t mode, double vad_threshold, void *stream);
+
+/* Segmented per-collision-window arbitration — replaces the scoring + selection of
+ * performArbitration, audio_service.go:517-571, for n_windows windows at once.
+ * Window w owns members [seg_offsets[w], seg_offsets[w+1]) in join order.  Member m's
+ * wake-word buffer is d_samples[wake_off[m] .. +wake_n[m]) (RelayStream.WakeWordSignal).
+ * scores[m]  = calculateSignalStrength(wake buffer) for contending members (exact
+ *              reference order), untouched otherwise (:522-528);
+ * winner[w]  = member index (global, into the member arrays) chosen by the strict-`>`
+ *              running max from 0.0 (:519,:535), first member if none exceeded 0 (:542-547),
+ *              UINT32_MAX for an empty window;
+ * status_out[m] = GA_RELAY_WINNER / GA_RELAY_CANCELLED for every member (:553-571).
+ * wake_off entries must be multiples of 4 samples.  All arrays are device pointers. */
+int ga_k_arbitrate(const float *d_samples, const uint64_t *d_wake_off, const uint32_t *d_wake_n,
+                   const uint8_t *d_status_in, const uint32_t *d_seg_offsets, uint32_t n_windows,
+                   uint32_t n_members, double *d_scores, uint32_t *d_winner, uint8_t *d_status_out,
+                   void *stream);
+
+/* Scores only: calculateSignalStrength (audio_service.go:818-852) of n_members buffers.
+ * d_stats (nullable) receives the logged side statistics {sumsq, rms, n_samples, nonzero,
+ * peak} per member; its digest bytes are left untouched. */
+int ga_k_signal_strength(const float *d_samples, const uint64_t *d_wake_off, const uint32_t *d_wake_n,
+                         const uint8_t *d_status_in, uint32_t n_members, double *d_scores,
+                         ga_result *d_stats, void *stream);
+
+/* Selection only, from precomputed scores (cross-shard windows: the scores arrive as
+ * exchanged records).  Same rules as above. */
+int ga_k_select(const double *d_scores, const uint8_t *d_status_in, const uint32_t *d_seg_offsets,
+                uint32_t n_windows, uint32_t *d_winner, uint8_t *d_status_out, void *stream);
+
+/* Cross-shard windows: scatter scores that arrived from other shards
+ * (d_gathered, the all-gathered guest scores) into this shard's member slots:
+ * d_scores[dst_slot[i]] = d_gathered[src_idx[i]].  Runs between the scoring launch and
+ * ga_k_select.  No reference counterpart: the reference is a single process. */
+int ga_k_route_scores(const double *d_gathered, const uint32_t *d_src_idx,
+                      const uint32_t *d_dst_slot, uint32_t n, double *d_scores, void *stream);
+
+/* ===================================================================== context
+ * Host-buffer layer: what internal/gpuaudio binds.  One context per GPU.        */
+
+typedef struct ga_ctx ga_ctx;
+
+typedef struct ga_config {
+    int32_t  device;            /* CUDA ordinal                                        */
+    uint32_t max_streams;       /* dense stream slots                                  */
+    uint32_t max_batch_msgs;    /* largest n accepted by one ga_submit                 */
+    uint32_t max_inflight;      /* tickets that may be outstanding (>= 1)              */
+    uint64_t ring_bytes;        /* pinned host ring == device PCM slab size            */
+    uint64_t arena_samples;     /* f32 samples kept per stream (wake word + speech);
+                                   multiple of 4                                       */
+    uint64_t wake_samples_max;  /* of which reserved for RelayStream.WakeWordSignal;
+                                   multiple of 4, < arena_samples                      */
+    uint32_t mode;              /* GA_DO_* bits                                        */
+    uint32_t want_frames;       /* != 0: per-frame records are produced and returned   */
+    double   vad_threshold;     /* VAD flag = rms > threshold (default 0.01)           */
+} ga_config;
+
+/* audio_service.go:233-244 is where the hub would call this (createAudioService). */
+int  ga_init(const ga_config *cfg, ga_ctx **out);
+void ga_shutdown(ga_ctx *ctx);
+const char *ga_last_error(void);
+
+/* Reserve nbytes (rounded up to 16) in the C-owned pinned ring; the caller copies
+ * chunk.AudioData there (audio_service.go:964, :999 hand the bytes over here instead of
+ * converting them inline).  Callable concurrently from many threads (lock-free).
+ * ring_offset is a monotonically increasing virtual offset (the library wraps it);
+ * waiting a ticket releases the ring up to the highest offset that ticket contained, so
+ * the batching goroutine submits reservations in offset order. */
+int ga_ring_reserve(ga_ctx *ctx, uint64_t nbytes, void **host_ptr, uint64_t *ring_offset);
+
+typedef struct ga_msg {
+    uint64_t ring_offset;  /* virtual offset from ga_ring_reserve                       */
+    uint32_t nbytes;
+    uint32_t stream_id;
+    uint32_t flags;        /* GA_MSG_*                                                  */
+    uint32_t reserved;
+} ga_msg;
+
+/* One batch tick: H2D of the ring range + descriptors, the fused ingest launch, D2H of
+ * the result records — all asynchronous.  Messages of one stream must appear in arrival
+ * order.  Returns a ticket.  Called by the single batching goroutine. */
+int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *ticket);
+
+/* Block until the ticket's results are on the host, then copy them out (results[n],
+ * frames[] if the context wants frames — sized by ga_ticket_frames) and release the
+ * ticket's ring range.  Tickets must be waited in submission order. */
+int ga_wait(ga_ctx *ctx, uint64_t ticket, ga_result *results, ga_frame *frames);
+int ga_ticket_frames(ga_ctx *ctx, uint64_t ticket, uint32_t *n_frames);
+
+/* Copy a stream's converted samples [first, first+n) to the host — what
+ * RelayStream.WakeWordSignal ++ SpeechAudio holds (audio_service.go:592-594); used for
+ * arbitration winners only. */
+int ga_fetch_samples(ga_ctx *ctx, uint32_t stream_id, uint64_t first, uint64_t n, float *out);
+int ga_stream_info(ga_ctx *ctx, uint32_t stream_id, uint64_t *n_samples, uint64_t *wake_samples);
+int ga_stream_reset(ga_ctx *ctx, uint32_t stream_id);
+
+/* performArbitration for many windows (audio_service.go:505-571).  Host arrays:
+ * seg_offsets[n_windows+1], stream_ids / status_in / scores / status_out per member,
+ * winner_idx[n_windows] (member index, UINT32_MAX for an empty window).  A member's wake
+ * buffer is the samples its GA_MSG_WAKE messages produced. */
+int ga_arbitrate(ga_ctx *ctx, const uint32_t *seg_offsets, uint32_t n_windows,
+                 const uint32_t *stream_ids, const uint8_t *status_in,
+                 uint32_t *winner_idx, double *scores, uint8_t *status_out);
+
+/* --------------------------------------------------------------- one-shot mirrors
+ * Same argument meaning and degenerate-input behaviour as the Go functions; used by
+ * the parity tests and by callers that have a single buffer. */
+
+/* bytesToFloat32Array(data) — audio_service.go:1048-1101.  Writes len/2 samples to out
+ * (odd trailing byte dropped, empty input -> 0 samples, never an error); res may be NULL. */
+int ga_bytes_to_float32(ga_ctx *ctx, const uint8_t *data, size_t len, float *out,
+                        size_t *n_out, ga_result *res);
+/* calculateSignalStrength(samples) — audio_service.go:818-852.  Empty -> rms 0.0. */
+int ga_signal_strength(ga_ctx *ctx, const float *samples, size_t n, double *rms, ga_result *res);
+/* SHA-256 of an arbitrary host byte string (the fingerprint hook, events/voice_event.go:84-88). */
+int ga_sha256(ga_ctx *ctx, const uint8_t *data, size_t len, uint8_t digest[32]);
+
+/* ===================================================================== utilities */
+
+/* Synthetic relay PCM: integer-only, bit-identical on host and device.
+ * Fills n_samples int16 samples of relay view (group, relay) starting at sample index
+ * `first`, for an utterance of utt_samples samples. */
+int ga_synth_fill_host(int16_t *out, uint64_t seed, uint32_t group, uint32_t relay,
+                       uint32_t first, uint32_t n_samples, uint32_t utt_samples);
+/* Fill a whole time-major batch on the device: message m of stream s (= group*group_size
+ * + relay, group offset by group_base) at d_pcm + (m*n_streams + s)*msg_samples*2. */
+int ga_synth_fill_batch_device(void *d_pcm, uint64_t seed, uint32_t group_base,
+                               uint32_t n_streams, uint32_t group_size, uint32_t n_msgs,
+                               uint32_t msg_samples, void *stream);
+
+/* As above with an explicit (group, relay) per stream slot (sharded layouts). */
+int ga_synth_fill_batch_device_map(void *d_pcm, uint64_t seed, const uint32_t *d_group,
+                                   const uint32_t *d_relay, uint32_t n_streams, uint32_t n_msgs,
+                                   uint32_t msg_samples, void *stream);
+/* Same batch layout, filled on the host with n_threads workers (CPU-baseline input). */
+int ga_synth_fill_batch_host(void *pcm, uint64_t seed, uint32_t group_base, uint32_t n_streams,
+                             uint32_t group_size, uint32_t n_msgs, uint32_t msg_samples,
+                             uint32_t n_threads);
+
+/* Introspection for harnesses. */
+uint64_t ga_launch_count(void);            /* kernels launched by this library so far */
+int      ga_abi_version(void);
+/* sizes of {ga_result, ga_frame, ga_desc, ga_msg, ga_config} for binding self-checks */
+void     ga_abi_sizes(uint32_t out[5]);
+int      ga_device_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPUAUDIO_H */

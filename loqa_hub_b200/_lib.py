@@ -1,0 +1,117 @@
+"""ctypes binding of libgpuaudio.so (include/gpuaudio.h).
+
+The library is the product; this module only declares its C ABI.  Loading fails
+loudly when the shared object is missing — there is no Python or CPU fallback.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(HERE, "libgpuaudio.so")
+
+GA_OK = 0
+GA_ERR_ARG, GA_ERR_CUDA, GA_ERR_NOMEM, GA_ERR_RING_FULL = -1, -2, -3, -4
+GA_ERR_OVERFLOW, GA_ERR_STATE, GA_ERR_COMM = -5, -6, -7
+RELAY_CONNECTED, RELAY_CONTENDING, RELAY_WINNER, RELAY_CANCELLED = 0, 1, 2, 3
+MSG_WAKE, MSG_EOS, MSG_FIRST = 1, 2, 4
+DO_CONVERT, DO_FEATURES, DO_SHA256, DO_ALL = 1, 2, 4, 7
+FRAME_SAMPLES = 320
+NO_WINNER = 0xFFFFFFFF
+
+RESULT_DTYPE = np.dtype([("digest", "u1", 32), ("sumsq", "<f8"), ("rms", "<f8"),
+                         ("n_samples", "<u4"), ("nonzero", "<u4"), ("peak", "<f4"),
+                         ("flags", "<u4")])
+FRAME_DTYPE = np.dtype([("sumsq", "<f8"), ("rms", "<f8"), ("n_samples", "<u4"),
+                        ("nonzero", "<u4"), ("peak", "<f4"), ("vad", "<u4")])
+DESC_DTYPE = np.dtype([("in_off", "<u8"), ("out_off", "<u8"), ("nbytes", "<u4"),
+                       ("stream_id", "<u4"), ("flags", "<u4"), ("frame_off", "<u4")])
+MSG_DTYPE = np.dtype([("ring_offset", "<u8"), ("nbytes", "<u4"), ("stream_id", "<u4"),
+                      ("flags", "<u4"), ("reserved", "<u4")])
+assert RESULT_DTYPE.itemsize == 64 and FRAME_DTYPE.itemsize == 32
+assert DESC_DTYPE.itemsize == 32 and MSG_DTYPE.itemsize == 24
+
+
+class Config(C.Structure):
+    _fields_ = [("device", C.c_int32), ("max_streams", C.c_uint32), ("max_batch_msgs", C.c_uint32),
+                ("max_inflight", C.c_uint32), ("ring_bytes", C.c_uint64), ("arena_samples", C.c_uint64),
+                ("wake_samples_max", C.c_uint64), ("mode", C.c_uint32), ("want_frames", C.c_uint32),
+                ("vad_threshold", C.c_double)]
+
+
+# every symbol include/gpuaudio.h declares: name -> (restype, argtypes)
+_vp, _u32, _u64, _i32, _sz = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int, C.c_size_t
+SYMBOLS = {
+    "ga_k_ingest": (_i32, [_vp, _vp, _u32, _vp, _vp, _vp, _u32, C.c_double, _vp]),
+    "ga_k_arbitrate": (_i32, [_vp, _vp, _vp, _vp, _vp, _u32, _u32, _vp, _vp, _vp, _vp]),
+    "ga_k_signal_strength": (_i32, [_vp, _vp, _vp, _vp, _u32, _vp, _vp, _vp]),
+    "ga_k_select": (_i32, [_vp, _vp, _vp, _u32, _vp, _vp, _vp]),
+    "ga_k_route_scores": (_i32, [_vp, _vp, _vp, _u32, _vp, _vp]),
+    "ga_init": (_i32, [C.POINTER(Config), C.POINTER(_vp)]),
+    "ga_shutdown": (None, [_vp]),
+    "ga_last_error": (C.c_char_p, []),
+    "ga_ring_reserve": (_i32, [_vp, _u64, C.POINTER(_vp), C.POINTER(_u64)]),
+    "ga_submit": (_i32, [_vp, _vp, _u32, C.POINTER(_u64)]),
+    "ga_wait": (_i32, [_vp, _u64, _vp, _vp]),
+    "ga_ticket_frames": (_i32, [_vp, _u64, C.POINTER(_u32)]),
+    "ga_fetch_samples": (_i32, [_vp, _u32, _u64, _u64, _vp]),
+    "ga_stream_info": (_i32, [_vp, _u32, C.POINTER(_u64), C.POINTER(_u64)]),
+    "ga_stream_reset": (_i32, [_vp, _u32]),
+    "ga_arbitrate": (_i32, [_vp, _vp, _u32, _vp, _vp, _vp, _vp, _vp]),
+    "ga_bytes_to_float32": (_i32, [_vp, _vp, _sz, _vp, C.POINTER(_sz), _vp]),
+    "ga_signal_strength": (_i32, [_vp, _vp, _sz, C.POINTER(C.c_double), _vp]),
+    "ga_sha256": (_i32, [_vp, _vp, _sz, _vp]),
+    "ga_synth_fill_host": (_i32, [_vp, _u64, _u32, _u32, _u32, _u32, _u32]),
+    "ga_synth_fill_batch_device": (_i32, [_vp, _u64, _u32, _u32, _u32, _u32, _u32, _vp]),
+    "ga_synth_fill_batch_device_map": (_i32, [_vp, _u64, _vp, _vp, _u32, _u32, _u32, _vp]),
+    "ga_synth_fill_batch_host": (_i32, [_vp, _u64, _u32, _u32, _u32, _u32, _u32, _u32]),
+    "ga_launch_count": (_u64, []),
+    "ga_abi_version": (_i32, []),
+    "ga_abi_sizes": (None, [C.POINTER(_u32 * 5)]),
+    "ga_device_count": (_i32, []),
+}
+
+_lib = None
+
+
+class GpuAudioError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("libgpuaudio error %d: %s" % (code, msg))
+        self.code = code
+
+
+def load():
+    """Load libgpuaudio.so and bind every declared symbol.  Raises if it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(SO_PATH):
+        raise ImportError(
+            "%s not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a). libgpuaudio has no CPU fallback." % SO_PATH)
+    lib = C.CDLL(SO_PATH)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)      # AttributeError if the .so does not export it
+        fn.restype = res
+        fn.argtypes = args
+    sizes = (_u32 * 5)()
+    lib.ga_abi_sizes(C.byref(sizes))
+    want = [RESULT_DTYPE.itemsize, FRAME_DTYPE.itemsize, DESC_DTYPE.itemsize, MSG_DTYPE.itemsize,
+            C.sizeof(Config)]
+    if list(sizes) != want:
+        raise ImportError("libgpuaudio ABI struct sizes %s != binding %s" % (list(sizes), want))
+    _lib = lib
+    return lib
+
+
+def check(rc):
+    if rc != GA_OK:
+        raise GpuAudioError(rc, load().ga_last_error().decode("utf-8", "replace"))
+
+
+def ptr(a):
+    """void* of a numpy array (None for empty / None)."""
+    if a is None:
+        return None
+    return a.ctypes.data_as(C.c_void_p) if a.size else None

@@ -1,0 +1,232 @@
+// arbitrate.cu — segmented per-collision-window arbitration for B200 (sm_100a).
+//
+// Replaces the scoring and selection of performArbitration
+// (internal/grpc/audio_service.go:505-571) for many windows per launch:
+//   score_kernel : calculateSignalStrength (:818-852) of every contending member's
+//                  wake-word buffer.  The reference sums float64(float32(s*s)) strictly in
+//                  index order and the winner must never differ, so each LANE owns one
+//                  member and adds its samples sequentially; the 32 members of a warp tile
+//                  are streamed through shared memory with one TMA bulk copy per member
+//                  per slice so global reads stay coalesced 512-byte bursts.
+//   select_kernel: per window, the reference's loop — skip non-contending (:522-524),
+//                  strict `>` against a running max that starts at 0.0 (:519, :535), first
+//                  member when nothing exceeded 0.0 (:542-547) — then Winner / Cancelled
+//                  for every member (:553-571).  Join order stands in for Go's random map
+//                  iteration order.
+#include "common.cuh"
+
+namespace ga {
+
+constexpr int kArbWarps = 2;
+constexpr int kArbSlice = 512;                  // bytes of f32 per member per stage
+constexpr int kArbStages = 2;
+constexpr int kArbRowStride = kArbSlice + 16;   // 33 x 16 B: conflict-free lane-per-row LDS.128
+constexpr int kArbStageBytes = 32 * kArbRowStride;
+constexpr int kArbWarpBytes = kArbStages * kArbStageBytes + 128;
+
+__global__ void __launch_bounds__(kArbWarps * 32)
+score_kernel(const float *__restrict__ samples, const uint64_t *__restrict__ wake_off,
+             const uint32_t *__restrict__ wake_n, const uint8_t *__restrict__ status_in,
+             uint32_t n_members, double *__restrict__ scores, ga_result *__restrict__ stats)
+{
+    constexpr uint32_t FULL = 0xffffffffu;
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint8_t *wbase = smem + warp * kArbWarpBytes;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(wbase + kArbStages * kArbStageBytes);
+    if (lane == 0) {
+        for (int s = 0; s < kArbStages; s++) mbar_init(&bars[s], 1);
+        fence_mbar_init();
+    }
+    __syncwarp();
+
+    const uint32_t n_tiles = (n_members + 31) / 32;
+    uint32_t it = 0;
+    for (uint32_t tile = blockIdx.x * kArbWarps + warp; tile < n_tiles; tile += gridDim.x * kArbWarps) {
+        const uint32_t m = tile * 32 + lane;
+        const bool active = m < n_members && (!status_in || status_in[m] == GA_RELAY_CONTENDING);
+        const uint32_t n = active ? wake_n[m] : 0;
+        const uint8_t *src = reinterpret_cast<const uint8_t *>(samples + (active ? wake_off[m] : 0));
+        const uint32_t nbytes = n * 4u;
+        const uint32_t my_nch = (nbytes + kArbSlice - 1) / kArbSlice;
+        const uint32_t nch = __reduce_max_sync(FULL, my_nch);
+
+        auto issue = [&](uint32_t c, uint32_t job) {
+            const int stage = job % kArbStages;
+            const uint32_t lo = c * kArbSlice;
+            uint32_t bytes = nbytes > lo ? min(nbytes - lo, static_cast<uint32_t>(kArbSlice)) : 0u;
+            bytes = (bytes + 15u) & ~15u;
+            const uint32_t total = __reduce_add_sync(FULL, bytes);
+            if (lane == 0) mbar_arrive_expect_tx(&bars[stage], total);
+            __syncwarp();
+            if (bytes) bulk_g2s(wbase + stage * kArbStageBytes + lane * kArbRowStride, src + lo, bytes, &bars[stage]);
+        };
+
+        for (uint32_t c = 0; c < nch && c < kArbStages; c++) issue(c, it + c);
+        double sum = 0.0;
+        uint32_t nz = 0;       // side statistics the reference logs (:829-838)
+        float peak = 0.0f;
+        auto add = [&](float x) {
+            sum += sq_f64(x);
+            nz += (x != 0.0f);
+            peak = fmaxf(peak, fabsf(x));
+        };
+        for (uint32_t c = 0; c < nch; c++) {
+            const uint32_t job = it + c;
+            const int stage = job % kArbStages;
+            mbar_wait(&bars[stage], (job / kArbStages) & 1u);
+            const uint32_t lo = c * (kArbSlice / 4);
+            if (lo < n) {
+                const uint32_t cnt = min(n - lo, static_cast<uint32_t>(kArbSlice / 4));
+                const float4 *row = reinterpret_cast<const float4 *>(wbase + stage * kArbStageBytes + lane * kArbRowStride);
+                uint32_t k = 0;
+                for (; k + 4 <= cnt; k += 4) {
+                    const float4 v = row[k >> 2];
+                    add(v.x); add(v.y); add(v.z); add(v.w);
+                }
+                if (k < cnt) {
+                    const float4 v = row[k >> 2];
+                    add(v.x);
+                    if (k + 1 < cnt) add(v.y);
+                    if (k + 2 < cnt) add(v.z);
+                }
+            }
+            __syncwarp();
+            if (c + kArbStages < nch) issue(c + kArbStages, job + kArbStages);
+        }
+        it += nch;
+        if (active) {   // :841; empty buffer -> 0.0 (:819-822)
+            const double rms = n ? __dsqrt_rn(__ddiv_rn(sum, static_cast<double>(n))) : 0.0;
+            scores[m] = rms;
+            if (stats) {
+                ga_result *r = stats + m;
+                r->sumsq = sum; r->rms = rms; r->n_samples = n; r->nonzero = nz; r->peak = peak; r->flags = 0;
+            }
+        }
+    }
+}
+
+__global__ void select_kernel(const double *__restrict__ scores, const uint8_t *__restrict__ status_in,
+                              const uint32_t *__restrict__ seg, uint32_t n_windows,
+                              uint32_t *__restrict__ winner, uint8_t *__restrict__ status_out)
+{
+    const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= n_windows) return;
+    const uint32_t a = seg[w], b = seg[w + 1];
+    uint32_t win = 0xffffffffu;
+    double best = 0.0;                                            // :519
+    for (uint32_t m = a; m < b; m++) {                            // :521 (join order)
+        if (status_in[m] != GA_RELAY_CONTENDING) continue;        // :522-524
+        const double s = scores[m];
+        if (s > best) { best = s; win = m; }                      // :535 strict >
+    }
+    if (win == 0xffffffffu && b > a) win = a;                     // :542-547
+    winner[w] = win;
+    for (uint32_t m = a; m < b; m++)                              // :553-571
+        status_out[m] = (m == win) ? GA_RELAY_WINNER : GA_RELAY_CANCELLED;
+}
+
+__global__ void route_kernel(const double *__restrict__ gathered, const uint32_t *__restrict__ src,
+                             const uint32_t *__restrict__ dst, uint32_t n, double *__restrict__ scores)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) scores[dst[i]] = gathered[src[i]];
+}
+
+static int launch_select(const double *d_scores, const uint8_t *d_status_in, const uint32_t *d_seg,
+                         uint32_t n_windows, uint32_t *d_winner, uint8_t *d_status_out, cudaStream_t st)
+{
+    if (n_windows == 0) return GA_OK;
+    const int threads = 128;
+    select_kernel<<<(n_windows + threads - 1) / threads, threads, 0, st>>>(d_scores, d_status_in, d_seg,
+                                                                          n_windows, d_winner, d_status_out);
+    GA_CHECK_LAUNCH("select_kernel");
+    return GA_OK;
+}
+
+}  // namespace ga
+
+extern "C" int ga_k_select(const double *d_scores, const uint8_t *d_status_in, const uint32_t *d_seg_offsets,
+                           uint32_t n_windows, uint32_t *d_winner, uint8_t *d_status_out, void *stream)
+{
+    using namespace ga;
+    if (n_windows && (!d_scores || !d_status_in || !d_seg_offsets || !d_winner || !d_status_out)) {
+        set_error("ga_k_select: NULL argument");
+        return GA_ERR_ARG;
+    }
+    return launch_select(d_scores, d_status_in, d_seg_offsets, n_windows, d_winner, d_status_out,
+                         static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int ga_k_route_scores(const double *d_gathered, const uint32_t *d_src_idx,
+                                 const uint32_t *d_dst_slot, uint32_t n, double *d_scores, void *stream)
+{
+    using namespace ga;
+    if (n == 0) return GA_OK;
+    if (!d_gathered || !d_src_idx || !d_dst_slot || !d_scores) { set_error("ga_k_route_scores: NULL argument"); return GA_ERR_ARG; }
+    route_kernel<<<(n + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(d_gathered, d_src_idx, d_dst_slot, n, d_scores);
+    GA_CHECK_LAUNCH("route_kernel");
+    return GA_OK;
+}
+
+static int launch_scores(const float *d_samples, const uint64_t *d_wake_off, const uint32_t *d_wake_n,
+                         const uint8_t *d_status_in, uint32_t n_members, double *d_scores,
+                         ga_result *d_stats, cudaStream_t st)
+{
+    using namespace ga;
+    if (n_members == 0) return GA_OK;
+    static thread_local int configured_dev = -1;
+    int dev = 0;
+    GA_CUDA_TRY(cudaGetDevice(&dev));
+    constexpr int smem = kArbWarps * kArbWarpBytes;
+    if (configured_dev != dev) {
+        GA_CUDA_TRY(cudaFuncSetAttribute(score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        configured_dev = dev;
+    }
+    const uint32_t n_tiles = (n_members + 31) / 32;
+    const uint32_t grid = (n_tiles + kArbWarps - 1) / kArbWarps;
+    score_kernel<<<grid, kArbWarps * 32, smem, st>>>(d_samples, d_wake_off, d_wake_n, d_status_in,
+                                                     n_members, d_scores, d_stats);
+    GA_CHECK_LAUNCH("score_kernel");
+    return GA_OK;
+}
+
+extern "C" int ga_k_signal_strength(const float *d_samples, const uint64_t *d_wake_off,
+                                    const uint32_t *d_wake_n, const uint8_t *d_status_in,
+                                    uint32_t n_members, double *d_scores, ga_result *d_stats, void *stream)
+{
+    using namespace ga;
+    if (n_members == 0) return GA_OK;
+    if (!d_samples || !d_wake_off || !d_wake_n || !d_scores) {
+        set_error("ga_k_signal_strength: NULL argument");
+        return GA_ERR_ARG;
+    }
+    if (reinterpret_cast<uintptr_t>(d_samples) & 15u) {
+        set_error("ga_k_signal_strength: d_samples must be 16-byte aligned");
+        return GA_ERR_ARG;
+    }
+    return launch_scores(d_samples, d_wake_off, d_wake_n, d_status_in, n_members, d_scores, d_stats,
+                         static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int ga_k_arbitrate(const float *d_samples, const uint64_t *d_wake_off, const uint32_t *d_wake_n,
+                              const uint8_t *d_status_in, const uint32_t *d_seg_offsets, uint32_t n_windows,
+                              uint32_t n_members, double *d_scores, uint32_t *d_winner,
+                              uint8_t *d_status_out, void *stream)
+{
+    using namespace ga;
+    if (n_windows == 0) return GA_OK;
+    if (!d_seg_offsets || !d_winner) { set_error("ga_k_arbitrate: NULL argument"); return GA_ERR_ARG; }
+    if (n_members && (!d_samples || !d_wake_off || !d_wake_n || !d_status_in || !d_scores || !d_status_out)) {
+        set_error("ga_k_arbitrate: NULL argument");
+        return GA_ERR_ARG;
+    }
+    if (reinterpret_cast<uintptr_t>(d_samples) & 15u) {
+        set_error("ga_k_arbitrate: d_samples must be 16-byte aligned");
+        return GA_ERR_ARG;
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int rc = launch_scores(d_samples, d_wake_off, d_wake_n, d_status_in, n_members, d_scores, nullptr, st);
+    if (rc) return rc;
+    return launch_select(d_scores, d_status_in, d_seg_offsets, n_windows, d_winner, d_status_out, st);
+}

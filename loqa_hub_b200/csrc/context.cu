@@ -1,0 +1,692 @@
+// context.cu — host side of libgpuaudio: the C-owned pinned ring, batch submit/wait,
+// the per-stream sample arena, and the one-shot mirrors of the Go functions.
+//
+// This is the layer the cgo package internal/gpuaudio binds.  It keeps the
+// reference's observable behaviour for the path: degenerate inputs (empty / odd-length
+// chunks, empty wake-word buffers) produce empty / 0.0 results and never an error
+// (internal/grpc/audio_service.go:1050-1063, :819-822); errors are reserved for misuse of
+// the boundary and CUDA failures.  There is no CPU fallback anywhere in this file.
+#include <algorithm>
+#include <atomic>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <thread>
+#include <vector>
+
+#include "common.cuh"
+#include "synth.h"
+
+namespace ga {
+
+// ---------------------------------------------------------------- errors / globals
+static thread_local char t_err[512] = "";
+std::atomic<uint64_t> g_launches{0};
+
+void set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(t_err, sizeof t_err, fmt, ap);
+    va_end(ap);
+}
+
+int num_sms(int *out)
+{
+    static thread_local int cached_dev = -1, cached = 0;
+    int dev = 0;
+    GA_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev != cached_dev) {
+        GA_CUDA_TRY(cudaDeviceGetAttribute(&cached, cudaDevAttrMultiProcessorCount, dev));
+        cached_dev = dev;
+    }
+    *out = cached;
+    return GA_OK;
+}
+
+// ---------------------------------------------------------------- context
+struct StreamState {
+    uint64_t wake_n = 0;     // samples in the wake-word region   (RelayStream.WakeWordSignal)
+    uint64_t speech_n = 0;   // samples in the speech region      (RelayStream.SpeechAudio)
+};
+
+struct Slot {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;
+    ga_desc *h_desc = nullptr, *d_desc = nullptr;
+    ga_result *h_res = nullptr, *d_res = nullptr;
+    ga_frame *h_frames = nullptr, *d_frames = nullptr;
+    uint64_t ticket = 0;
+    uint64_t release_to = 0;
+    uint32_t n_msgs = 0, n_frames = 0;
+    bool busy = false;
+};
+
+}  // namespace ga
+
+struct ga_ctx {
+    ga_config cfg;
+    uint8_t *h_ring = nullptr, *d_ring = nullptr;
+    float *d_arena = nullptr;
+    uint64_t frames_cap = 0;
+    std::atomic<uint64_t> ring_head{0}, ring_tail{0};
+    std::vector<ga::StreamState> streams;
+    std::vector<ga::Slot> slots;
+    uint64_t next_ticket = 1, oldest_ticket = 1;
+    std::mutex mu;   // guards submit/wait/arbitrate bookkeeping (not the ring reserve path)
+    // scratch for ga_arbitrate
+    cudaStream_t aux = nullptr;
+};
+
+namespace ga {
+
+static int set_device(const ga_ctx *ctx)
+{
+    GA_CUDA_TRY(cudaSetDevice(ctx->cfg.device));
+    return GA_OK;
+}
+
+static void destroy(ga_ctx *c)
+{
+    if (!c) return;
+    cudaSetDevice(c->cfg.device);
+    for (auto &s : c->slots) {
+        if (s.stream) cudaStreamSynchronize(s.stream);
+        if (s.done) cudaEventDestroy(s.done);
+        if (s.h_desc) cudaFreeHost(s.h_desc);
+        if (s.d_desc) cudaFree(s.d_desc);
+        if (s.h_res) cudaFreeHost(s.h_res);
+        if (s.d_res) cudaFree(s.d_res);
+        if (s.h_frames) cudaFreeHost(s.h_frames);
+        if (s.d_frames) cudaFree(s.d_frames);
+        if (s.stream) cudaStreamDestroy(s.stream);
+    }
+    if (c->aux) cudaStreamDestroy(c->aux);
+    if (c->h_ring) cudaFreeHost(c->h_ring);
+    if (c->d_ring) cudaFree(c->d_ring);
+    if (c->d_arena) cudaFree(c->d_arena);
+    delete c;
+}
+
+#define GA_ALLOC_TRY(expr)                                                            \
+    do {                                                                              \
+        cudaError_t _e = (expr);                                                      \
+        if (_e != cudaSuccess) {                                                      \
+            ga::set_error("%s failed: %s", #expr, cudaGetErrorString(_e));            \
+            cudaGetLastError();                                                       \
+            ga::destroy(c);                                                           \
+            return _e == cudaErrorMemoryAllocation ? GA_ERR_NOMEM : GA_ERR_CUDA;      \
+        }                                                                             \
+    } while (0)
+
+}  // namespace ga
+
+using namespace ga;
+
+extern "C" const char *ga_last_error(void) { return t_err; }
+extern "C" uint64_t ga_launch_count(void) { return g_launches.load(); }
+extern "C" int ga_abi_version(void) { return GA_ABI_VERSION; }
+extern "C" void ga_abi_sizes(uint32_t out[5])
+{
+    out[0] = sizeof(ga_result); out[1] = sizeof(ga_frame); out[2] = sizeof(ga_desc);
+    out[3] = sizeof(ga_msg); out[4] = sizeof(ga_config);
+}
+extern "C" int ga_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+static_assert(sizeof(ga_result) == 64, "ga_result layout");
+static_assert(sizeof(ga_frame) == 32, "ga_frame layout");
+static_assert(sizeof(ga_desc) == 32, "ga_desc layout");
+static_assert(sizeof(ga_msg) == 24, "ga_msg layout");
+
+extern "C" int ga_init(const ga_config *cfg, ga_ctx **out)
+{
+    if (!cfg || !out) { set_error("ga_init: NULL argument"); return GA_ERR_ARG; }
+    *out = nullptr;
+    if (cfg->max_streams == 0 || cfg->max_batch_msgs == 0 || cfg->ring_bytes < 4096 ||
+        (cfg->ring_bytes & 15u) || (cfg->mode & GA_DO_ALL) == 0) {
+        set_error("ga_init: bad config (streams/batch/ring/mode)");
+        return GA_ERR_ARG;
+    }
+    if ((cfg->mode & GA_DO_CONVERT) &&
+        (cfg->arena_samples == 0 || (cfg->arena_samples & 3u) || (cfg->wake_samples_max & 3u) ||
+         cfg->wake_samples_max >= cfg->arena_samples)) {
+        set_error("ga_init: arena_samples / wake_samples_max must be multiples of 4 with wake < arena");
+        return GA_ERR_ARG;
+    }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        set_error("ga_init: no usable CUDA device (%s); this library has no CPU fallback",
+                  e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+        return GA_ERR_CUDA;
+    }
+    if (cfg->device < 0 || cfg->device >= ndev) { set_error("ga_init: device %d out of range", cfg->device); return GA_ERR_ARG; }
+    ga_ctx *c = new (std::nothrow) ga_ctx;
+    if (!c) { set_error("ga_init: out of host memory"); return GA_ERR_NOMEM; }
+    c->cfg = *cfg;
+    if (c->cfg.max_inflight == 0) c->cfg.max_inflight = 1;
+    if (c->cfg.vad_threshold == 0.0) c->cfg.vad_threshold = 0.01;
+    GA_ALLOC_TRY(cudaSetDevice(cfg->device));
+    GA_ALLOC_TRY(cudaHostAlloc(reinterpret_cast<void **>(&c->h_ring), cfg->ring_bytes, cudaHostAllocDefault));
+    GA_ALLOC_TRY(cudaMalloc(reinterpret_cast<void **>(&c->d_ring), cfg->ring_bytes + 16));
+    if (cfg->mode & GA_DO_CONVERT) {
+        const uint64_t arena = static_cast<uint64_t>(cfg->max_streams) * cfg->arena_samples;
+        GA_ALLOC_TRY(cudaMalloc(reinterpret_cast<void **>(&c->d_arena), (arena + 4) * sizeof(float)));
+    }
+    try {
+        c->streams.resize(cfg->max_streams);
+        c->slots.resize(c->cfg.max_inflight);
+    } catch (...) {
+        set_error("ga_init: out of host memory");
+        destroy(c);
+        return GA_ERR_NOMEM;
+    }
+    c->frames_cap = cfg->want_frames ? cfg->max_batch_msgs + cfg->ring_bytes / (2 * GA_FRAME_SAMPLES) : 0;
+    for (auto &s : c->slots) {
+        GA_ALLOC_TRY(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+        GA_ALLOC_TRY(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+        GA_ALLOC_TRY(cudaHostAlloc(reinterpret_cast<void **>(&s.h_desc), sizeof(ga_desc) * cfg->max_batch_msgs, cudaHostAllocDefault));
+        GA_ALLOC_TRY(cudaMalloc(reinterpret_cast<void **>(&s.d_desc), sizeof(ga_desc) * cfg->max_batch_msgs));
+        GA_ALLOC_TRY(cudaHostAlloc(reinterpret_cast<void **>(&s.h_res), sizeof(ga_result) * cfg->max_batch_msgs, cudaHostAllocDefault));
+        GA_ALLOC_TRY(cudaMalloc(reinterpret_cast<void **>(&s.d_res), sizeof(ga_result) * cfg->max_batch_msgs));
+        if (c->frames_cap) {
+            GA_ALLOC_TRY(cudaHostAlloc(reinterpret_cast<void **>(&s.h_frames), sizeof(ga_frame) * c->frames_cap, cudaHostAllocDefault));
+            GA_ALLOC_TRY(cudaMalloc(reinterpret_cast<void **>(&s.d_frames), sizeof(ga_frame) * c->frames_cap));
+        }
+    }
+    GA_ALLOC_TRY(cudaStreamCreateWithFlags(&c->aux, cudaStreamNonBlocking));
+    *out = c;
+    return GA_OK;
+}
+
+extern "C" void ga_shutdown(ga_ctx *ctx) { destroy(ctx); }
+
+// ---------------------------------------------------------------- pinned ring (lock-free MPSC bump)
+extern "C" int ga_ring_reserve(ga_ctx *ctx, uint64_t nbytes, void **host_ptr, uint64_t *ring_offset)
+{
+    if (!ctx || !host_ptr || !ring_offset) { set_error("ga_ring_reserve: NULL argument"); return GA_ERR_ARG; }
+    const uint64_t size = ctx->cfg.ring_bytes;
+    uint64_t need = (nbytes + 15u) & ~15ull;
+    if (need == 0) need = 16;
+    if (need > size) { set_error("ga_ring_reserve: %llu bytes exceed the ring", (unsigned long long)nbytes); return GA_ERR_ARG; }
+    uint64_t head = ctx->ring_head.load(std::memory_order_relaxed);
+    for (;;) {
+        uint64_t start = head;
+        const uint64_t phys = start % size;
+        if (phys + need > size) start += size - phys;          // never split a message across the wrap
+        const uint64_t end = start + need;
+        if (end - ctx->ring_tail.load(std::memory_order_acquire) > size) {
+            set_error("ga_ring_reserve: ring full (wait for outstanding tickets)");
+            return GA_ERR_RING_FULL;
+        }
+        if (ctx->ring_head.compare_exchange_weak(head, end, std::memory_order_acq_rel)) {
+            *ring_offset = start;
+            *host_ptr = ctx->h_ring + start % size;
+            return GA_OK;
+        }
+    }
+}
+
+// ---------------------------------------------------------------- submit / wait
+extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *ticket)
+{
+    if (!ctx || !ticket || (n && !msgs)) { set_error("ga_submit: NULL argument"); return GA_ERR_ARG; }
+    if (n > ctx->cfg.max_batch_msgs) { set_error("ga_submit: %u messages exceed max_batch_msgs %u", n, ctx->cfg.max_batch_msgs); return GA_ERR_OVERFLOW; }
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int rc = set_device(ctx);
+    if (rc) return rc;
+    Slot *slot = nullptr;
+    for (auto &s : ctx->slots) if (!s.busy) { slot = &s; break; }
+    if (!slot) { set_error("ga_submit: %u tickets already in flight", ctx->cfg.max_inflight); return GA_ERR_STATE; }
+
+    const uint64_t size = ctx->cfg.ring_bytes;
+    const uint64_t arena = ctx->cfg.arena_samples, wake_cap = ctx->cfg.wake_samples_max;
+    const bool convert = (ctx->cfg.mode & GA_DO_CONVERT) != 0;
+    const uint64_t head = ctx->ring_head.load(std::memory_order_acquire);
+    const uint64_t tail = ctx->ring_tail.load(std::memory_order_acquire);
+
+    // pass 1: validate (no state is touched until the whole batch is known to be good)
+    for (uint32_t i = 0; i < n; i++) {
+        const ga_msg &m = msgs[i];
+        const uint64_t need = (static_cast<uint64_t>(m.nbytes) + 15u) & ~15ull;
+        if (m.stream_id >= ctx->cfg.max_streams) { set_error("ga_submit: msg %u: stream_id %u out of range", i, m.stream_id); return GA_ERR_ARG; }
+        if ((m.ring_offset & 15u) || m.ring_offset < tail || m.ring_offset + need > head || m.ring_offset % size + need > size) {
+            set_error("ga_submit: msg %u: ring_offset %llu not a live reservation", i, (unsigned long long)m.ring_offset);
+            return GA_ERR_ARG;
+        }
+    }
+    // pass 2: descriptors.  Stream cursors are advanced on a scratch copy first.
+    struct Touched { uint32_t id; StreamState before; };
+    std::vector<Touched> undo;
+    uint64_t release_to = tail, frames = 0;
+    struct Run { uint64_t lo, hi; };
+    std::vector<Run> runs;
+    for (uint32_t i = 0; i < n; i++) {
+        const ga_msg &m = msgs[i];
+        StreamState &st = ctx->streams[m.stream_id];
+        undo.push_back({m.stream_id, st});
+        if (m.flags & GA_MSG_FIRST) st = StreamState();
+        const uint64_t ns = m.nbytes / 2;
+        ga_desc &d = slot->h_desc[i];
+        d.in_off = m.ring_offset % size;
+        d.nbytes = m.nbytes;
+        d.stream_id = m.stream_id;
+        d.flags = m.flags;
+        d.frame_off = static_cast<uint32_t>(frames);
+        d.out_off = 0;
+        if (convert) {
+            const uint64_t base = static_cast<uint64_t>(m.stream_id) * arena;
+            bool over;
+            if (m.flags & GA_MSG_WAKE) {           // audio_service.go:965 wakeWordBuffer = append(...)
+                over = st.wake_n + ns > wake_cap;
+                d.out_off = base + st.wake_n;
+                if (!over) st.wake_n += ns;
+            } else {                                // audio_service.go:1002 relay.SpeechAudio = append(...)
+                over = wake_cap + st.speech_n + ns > arena;
+                d.out_off = base + wake_cap + st.speech_n;
+                if (!over) st.speech_n += ns;
+            }
+            if (over) {
+                for (auto it = undo.rbegin(); it != undo.rend(); ++it) ctx->streams[it->id] = it->before;
+                set_error("ga_submit: msg %u overflows stream %u's sample arena", i, m.stream_id);
+                return GA_ERR_OVERFLOW;
+            }
+        } else if (m.flags & GA_MSG_WAKE) {
+            st.wake_n += ns;
+        } else {
+            st.speech_n += ns;
+        }
+        frames += (ns + GA_FRAME_SAMPLES - 1) / GA_FRAME_SAMPLES;
+        const uint64_t need = (static_cast<uint64_t>(m.nbytes) + 15u) & ~15ull;
+        release_to = std::max(release_to, m.ring_offset + need);
+        if (need) {
+            const uint64_t lo = d.in_off, hi = d.in_off + need;
+            if (!runs.empty() && lo >= runs.back().lo && lo <= runs.back().hi + 4096) runs.back().hi = std::max(runs.back().hi, hi);
+            else runs.push_back({lo, hi});
+        }
+    }
+    if (ctx->frames_cap && frames > ctx->frames_cap) {
+        for (auto it = undo.rbegin(); it != undo.rend(); ++it) ctx->streams[it->id] = it->before;
+        set_error("ga_submit: batch needs %llu frame records, capacity %llu", (unsigned long long)frames, (unsigned long long)ctx->frames_cap);
+        return GA_ERR_OVERFLOW;
+    }
+    if (runs.size() > 16) {   // scattered reservations: fall back to one covering copy
+        Run all = runs[0];
+        for (auto &r : runs) { all.lo = std::min(all.lo, r.lo); all.hi = std::max(all.hi, r.hi); }
+        runs.assign(1, all);
+    }
+
+    cudaStream_t s = slot->stream;
+    for (auto &r : runs)
+        GA_CUDA_TRY(cudaMemcpyAsync(ctx->d_ring + r.lo, ctx->h_ring + r.lo, r.hi - r.lo, cudaMemcpyHostToDevice, s));
+    if (n) {
+        GA_CUDA_TRY(cudaMemcpyAsync(slot->d_desc, slot->h_desc, sizeof(ga_desc) * n, cudaMemcpyHostToDevice, s));
+        rc = ga_k_ingest(ctx->d_ring, slot->d_desc, n, ctx->d_arena, slot->d_res,
+                         ctx->frames_cap ? slot->d_frames : nullptr, ctx->cfg.mode, ctx->cfg.vad_threshold, s);
+        if (rc) return rc;
+        GA_CUDA_TRY(cudaMemcpyAsync(slot->h_res, slot->d_res, sizeof(ga_result) * n, cudaMemcpyDeviceToHost, s));
+        if (ctx->frames_cap && frames)
+            GA_CUDA_TRY(cudaMemcpyAsync(slot->h_frames, slot->d_frames, sizeof(ga_frame) * frames, cudaMemcpyDeviceToHost, s));
+    }
+    GA_CUDA_TRY(cudaEventRecord(slot->done, s));
+    slot->busy = true;
+    slot->ticket = ctx->next_ticket++;
+    slot->n_msgs = n;
+    slot->n_frames = static_cast<uint32_t>(frames);
+    slot->release_to = release_to;
+    *ticket = slot->ticket;
+    return GA_OK;
+}
+
+static Slot *find_ticket(ga_ctx *ctx, uint64_t ticket)
+{
+    for (auto &s : ctx->slots) if (s.busy && s.ticket == ticket) return &s;
+    return nullptr;
+}
+
+extern "C" int ga_ticket_frames(ga_ctx *ctx, uint64_t ticket, uint32_t *n_frames)
+{
+    if (!ctx || !n_frames) { set_error("ga_ticket_frames: NULL argument"); return GA_ERR_ARG; }
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    Slot *s = find_ticket(ctx, ticket);
+    if (!s) { set_error("ga_ticket_frames: unknown ticket %llu", (unsigned long long)ticket); return GA_ERR_STATE; }
+    *n_frames = ctx->frames_cap ? s->n_frames : 0;
+    return GA_OK;
+}
+
+extern "C" int ga_wait(ga_ctx *ctx, uint64_t ticket, ga_result *results, ga_frame *frames)
+{
+    if (!ctx) { set_error("ga_wait: NULL context"); return GA_ERR_ARG; }
+    Slot *s;
+    {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        s = find_ticket(ctx, ticket);
+        if (!s) { set_error("ga_wait: unknown ticket %llu", (unsigned long long)ticket); return GA_ERR_STATE; }
+        if (ticket != ctx->oldest_ticket) {
+            set_error("ga_wait: tickets must be waited in submission order (oldest is %llu)", (unsigned long long)ctx->oldest_ticket);
+            return GA_ERR_STATE;
+        }
+        if (s->n_msgs && !results) { set_error("ga_wait: NULL results"); return GA_ERR_ARG; }
+    }
+    int rc = set_device(ctx);
+    if (rc) return rc;
+    GA_CUDA_TRY(cudaEventSynchronize(s->done));     // outside the lock: submit may proceed meanwhile
+    if (s->n_msgs) std::memcpy(results, s->h_res, sizeof(ga_result) * s->n_msgs);
+    if (frames && ctx->frames_cap && s->n_frames) std::memcpy(frames, s->h_frames, sizeof(ga_frame) * s->n_frames);
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    uint64_t t = ctx->ring_tail.load(std::memory_order_relaxed);
+    if (s->release_to > t) ctx->ring_tail.store(s->release_to, std::memory_order_release);
+    s->busy = false;
+    ctx->oldest_ticket = ticket + 1;
+    return GA_OK;
+}
+
+// every in-flight ingest must be visible to work queued on `st`
+static int join_inflight(ga_ctx *ctx, cudaStream_t st)
+{
+    for (auto &s : ctx->slots)
+        if (s.busy) GA_CUDA_TRY(cudaStreamWaitEvent(st, s.done, 0));
+    return GA_OK;
+}
+
+extern "C" int ga_stream_info(ga_ctx *ctx, uint32_t stream_id, uint64_t *n_samples, uint64_t *wake_samples)
+{
+    if (!ctx || stream_id >= ctx->cfg.max_streams) { set_error("ga_stream_info: bad argument"); return GA_ERR_ARG; }
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    const StreamState &st = ctx->streams[stream_id];
+    if (n_samples) *n_samples = st.wake_n + st.speech_n;
+    if (wake_samples) *wake_samples = st.wake_n;
+    return GA_OK;
+}
+
+extern "C" int ga_stream_reset(ga_ctx *ctx, uint32_t stream_id)
+{
+    if (!ctx || stream_id >= ctx->cfg.max_streams) { set_error("ga_stream_reset: bad argument"); return GA_ERR_ARG; }
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->streams[stream_id] = StreamState();   // cleanupRelay, audio_service.go:916-923
+    return GA_OK;
+}
+
+extern "C" int ga_fetch_samples(ga_ctx *ctx, uint32_t stream_id, uint64_t first, uint64_t n, float *out)
+{
+    if (!ctx || stream_id >= ctx->cfg.max_streams || (n && !out)) { set_error("ga_fetch_samples: bad argument"); return GA_ERR_ARG; }
+    if (!(ctx->cfg.mode & GA_DO_CONVERT)) { set_error("ga_fetch_samples: context does not materialise samples"); return GA_ERR_STATE; }
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int rc = set_device(ctx);
+    if (rc) return rc;
+    const StreamState st = ctx->streams[stream_id];
+    if (first + n > st.wake_n + st.speech_n) { set_error("ga_fetch_samples: range beyond the stream's %llu samples", (unsigned long long)(st.wake_n + st.speech_n)); return GA_ERR_ARG; }
+    rc = join_inflight(ctx, ctx->aux);
+    if (rc) return rc;
+    // logical order is WakeWordSignal ++ SpeechAudio (audio_service.go:592-594)
+    const float *base = ctx->d_arena + static_cast<uint64_t>(stream_id) * ctx->cfg.arena_samples;
+    uint64_t done = 0;
+    if (first < st.wake_n && n) {
+        const uint64_t k = std::min(n, st.wake_n - first);
+        GA_CUDA_TRY(cudaMemcpyAsync(out, base + first, k * sizeof(float), cudaMemcpyDeviceToHost, ctx->aux));
+        done = k;
+    }
+    if (done < n) {
+        const uint64_t sp_first = first + done - st.wake_n;
+        GA_CUDA_TRY(cudaMemcpyAsync(out + done, base + ctx->cfg.wake_samples_max + sp_first, (n - done) * sizeof(float), cudaMemcpyDeviceToHost, ctx->aux));
+    }
+    GA_CUDA_TRY(cudaStreamSynchronize(ctx->aux));
+    return GA_OK;
+}
+
+// ---------------------------------------------------------------- arbitration (host arrays)
+namespace {
+struct DevBuf {   // RAII for the transient device arrays of the host-array entry points
+    void *p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    int alloc(size_t bytes)
+    {
+        cudaError_t e = cudaMalloc(&p, bytes ? bytes : 16);
+        if (e != cudaSuccess) { cudaGetLastError(); set_error("cudaMalloc(%zu) failed: %s", bytes, cudaGetErrorString(e)); return GA_ERR_NOMEM; }
+        return GA_OK;
+    }
+    template <class T> T *as() { return static_cast<T *>(p); }
+};
+}  // namespace
+
+extern "C" int ga_arbitrate(ga_ctx *ctx, const uint32_t *seg_offsets, uint32_t n_windows,
+                            const uint32_t *stream_ids, const uint8_t *status_in,
+                            uint32_t *winner_idx, double *scores, uint8_t *status_out)
+{
+    if (!ctx) { set_error("ga_arbitrate: NULL context"); return GA_ERR_ARG; }
+    if (n_windows == 0) return GA_OK;
+    if (!seg_offsets || !winner_idx) { set_error("ga_arbitrate: NULL argument"); return GA_ERR_ARG; }
+    const uint32_t n_members = seg_offsets[n_windows];
+    if (n_members && (!stream_ids || !status_in || !scores || !status_out)) { set_error("ga_arbitrate: NULL member array"); return GA_ERR_ARG; }
+    if (!(ctx->cfg.mode & GA_DO_CONVERT)) { set_error("ga_arbitrate: context does not materialise samples"); return GA_ERR_STATE; }
+    for (uint32_t w = 0; w < n_windows; w++)
+        if (seg_offsets[w] > seg_offsets[w + 1]) { set_error("ga_arbitrate: seg_offsets not monotone at %u", w); return GA_ERR_ARG; }
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int rc = set_device(ctx);
+    if (rc) return rc;
+    std::vector<uint64_t> off(n_members);
+    std::vector<uint32_t> cnt(n_members);
+    for (uint32_t m = 0; m < n_members; m++) {
+        if (stream_ids[m] >= ctx->cfg.max_streams) { set_error("ga_arbitrate: member %u: stream_id out of range", m); return GA_ERR_ARG; }
+        off[m] = static_cast<uint64_t>(stream_ids[m]) * ctx->cfg.arena_samples;
+        cnt[m] = static_cast<uint32_t>(ctx->streams[stream_ids[m]].wake_n);
+    }
+    DevBuf d_off, d_cnt, d_st, d_seg, d_sc, d_win, d_so;
+    if ((rc = d_off.alloc(8ull * n_members)) || (rc = d_cnt.alloc(4ull * n_members)) || (rc = d_st.alloc(n_members)) ||
+        (rc = d_seg.alloc(4ull * (n_windows + 1))) || (rc = d_sc.alloc(8ull * n_members)) ||
+        (rc = d_win.alloc(4ull * n_windows)) || (rc = d_so.alloc(n_members)))
+        return rc;
+    cudaStream_t s = ctx->aux;
+    rc = join_inflight(ctx, s);
+    if (rc) return rc;
+    if (n_members) {
+        GA_CUDA_TRY(cudaMemcpyAsync(d_off.p, off.data(), 8ull * n_members, cudaMemcpyHostToDevice, s));
+        GA_CUDA_TRY(cudaMemcpyAsync(d_cnt.p, cnt.data(), 4ull * n_members, cudaMemcpyHostToDevice, s));
+        GA_CUDA_TRY(cudaMemcpyAsync(d_st.p, status_in, n_members, cudaMemcpyHostToDevice, s));
+        // scores of skipped relays stay what the caller passed in (audio_service.go:522-524)
+        GA_CUDA_TRY(cudaMemcpyAsync(d_sc.p, scores, 8ull * n_members, cudaMemcpyHostToDevice, s));
+    }
+    GA_CUDA_TRY(cudaMemcpyAsync(d_seg.p, seg_offsets, 4ull * (n_windows + 1), cudaMemcpyHostToDevice, s));
+    rc = ga_k_arbitrate(ctx->d_arena, d_off.as<uint64_t>(), d_cnt.as<uint32_t>(), d_st.as<uint8_t>(),
+                        d_seg.as<uint32_t>(), n_windows, n_members, d_sc.as<double>(), d_win.as<uint32_t>(),
+                        d_so.as<uint8_t>(), s);
+    if (rc) return rc;
+    if (n_members) {
+        GA_CUDA_TRY(cudaMemcpyAsync(scores, d_sc.p, 8ull * n_members, cudaMemcpyDeviceToHost, s));
+        GA_CUDA_TRY(cudaMemcpyAsync(status_out, d_so.p, n_members, cudaMemcpyDeviceToHost, s));
+    }
+    GA_CUDA_TRY(cudaMemcpyAsync(winner_idx, d_win.p, 4ull * n_windows, cudaMemcpyDeviceToHost, s));
+    GA_CUDA_TRY(cudaStreamSynchronize(s));
+    return GA_OK;
+}
+
+// ---------------------------------------------------------------- one-shot mirrors
+static int one_shot_ingest(ga_ctx *ctx, const uint8_t *data, size_t len, float *out, ga_result *res, uint32_t mode)
+{
+    if (len > 0xfffffff0ull) { set_error("one-shot message of %zu bytes exceeds the 4 GiB message limit", len); return GA_ERR_ARG; }
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int rc = set_device(ctx);
+    if (rc) return rc;
+    DevBuf d_pcm, d_out, d_desc, d_res;
+    const size_t padded = (len + 15u) & ~size_t(15);
+    const size_t ns = len / 2;
+    if ((rc = d_pcm.alloc(padded + 16)) || (rc = d_out.alloc((ns + 4) * sizeof(float))) ||
+        (rc = d_desc.alloc(sizeof(ga_desc))) || (rc = d_res.alloc(sizeof(ga_result))))
+        return rc;
+    ga_desc d{};
+    d.nbytes = static_cast<uint32_t>(len);
+    cudaStream_t s = ctx->aux;
+    if (len) GA_CUDA_TRY(cudaMemcpyAsync(d_pcm.p, data, len, cudaMemcpyHostToDevice, s));
+    GA_CUDA_TRY(cudaMemcpyAsync(d_desc.p, &d, sizeof d, cudaMemcpyHostToDevice, s));
+    rc = ga_k_ingest(d_pcm.p, d_desc.as<ga_desc>(), 1, d_out.as<float>(), d_res.as<ga_result>(), nullptr, mode,
+                     ctx->cfg.vad_threshold, s);
+    if (rc) return rc;
+    ga_result r;
+    GA_CUDA_TRY(cudaMemcpyAsync(&r, d_res.p, sizeof r, cudaMemcpyDeviceToHost, s));
+    if (out && ns) GA_CUDA_TRY(cudaMemcpyAsync(out, d_out.p, ns * sizeof(float), cudaMemcpyDeviceToHost, s));
+    GA_CUDA_TRY(cudaStreamSynchronize(s));
+    if (res) *res = r;
+    return GA_OK;
+}
+
+extern "C" int ga_bytes_to_float32(ga_ctx *ctx, const uint8_t *data, size_t len, float *out,
+                                   size_t *n_out, ga_result *res)
+{
+    if (!ctx || (len && !data) || (len >= 2 && !out)) { set_error("ga_bytes_to_float32: NULL argument"); return GA_ERR_ARG; }
+    if (n_out) *n_out = len / 2;
+    if (len == 0) {                       // audio_service.go:1050-1053: empty in, empty out, no error
+        if (res) std::memset(res, 0, sizeof *res);
+        return GA_OK;
+    }
+    return one_shot_ingest(ctx, data, len, out, res, GA_DO_CONVERT | GA_DO_FEATURES);
+}
+
+extern "C" int ga_sha256(ga_ctx *ctx, const uint8_t *data, size_t len, uint8_t digest[32])
+{
+    if (!ctx || (len && !data) || !digest) { set_error("ga_sha256: NULL argument"); return GA_ERR_ARG; }
+    ga_result r;
+    int rc = one_shot_ingest(ctx, data, len, nullptr, &r, GA_DO_SHA256);
+    if (rc) return rc;
+    std::memcpy(digest, r.digest, 32);
+    return GA_OK;
+}
+
+extern "C" int ga_signal_strength(ga_ctx *ctx, const float *samples, size_t n, double *rms, ga_result *res)
+{
+    if (!ctx || (n && !samples) || !rms) { set_error("ga_signal_strength: NULL argument"); return GA_ERR_ARG; }
+    if (n == 0) {                         // audio_service.go:819-822
+        *rms = 0.0;
+        if (res) std::memset(res, 0, sizeof *res);
+        return GA_OK;
+    }
+    if (n > 0x3fffffffull) { set_error("ga_signal_strength: %zu samples exceed the 2^30 limit", n); return GA_ERR_ARG; }
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int rc = set_device(ctx);
+    if (rc) return rc;
+    DevBuf d_s, d_off, d_cnt, d_sc, d_stats;
+    if ((rc = d_s.alloc((n + 4) * sizeof(float))) || (rc = d_off.alloc(8)) || (rc = d_cnt.alloc(4)) ||
+        (rc = d_sc.alloc(8)) || (rc = d_stats.alloc(sizeof(ga_result))))
+        return rc;
+    const uint64_t off = 0;
+    const uint32_t cnt = static_cast<uint32_t>(n);
+    cudaStream_t s = ctx->aux;
+    GA_CUDA_TRY(cudaMemcpyAsync(d_s.p, samples, n * sizeof(float), cudaMemcpyHostToDevice, s));
+    GA_CUDA_TRY(cudaMemcpyAsync(d_off.p, &off, 8, cudaMemcpyHostToDevice, s));
+    GA_CUDA_TRY(cudaMemcpyAsync(d_cnt.p, &cnt, 4, cudaMemcpyHostToDevice, s));
+    GA_CUDA_TRY(cudaMemsetAsync(d_stats.p, 0, sizeof(ga_result), s));
+    rc = ga_k_signal_strength(d_s.as<float>(), d_off.as<uint64_t>(), d_cnt.as<uint32_t>(), nullptr, 1,
+                              d_sc.as<double>(), d_stats.as<ga_result>(), s);
+    if (rc) return rc;
+    ga_result r;
+    GA_CUDA_TRY(cudaMemcpyAsync(&r, d_stats.p, sizeof r, cudaMemcpyDeviceToHost, s));
+    GA_CUDA_TRY(cudaMemcpyAsync(rms, d_sc.p, 8, cudaMemcpyDeviceToHost, s));
+    GA_CUDA_TRY(cudaStreamSynchronize(s));
+    if (res) *res = r;
+    return GA_OK;
+}
+
+// ---------------------------------------------------------------- synthetic PCM
+extern "C" int ga_synth_fill_host(int16_t *out, uint64_t seed, uint32_t group, uint32_t relay,
+                                  uint32_t first, uint32_t n_samples, uint32_t utt_samples)
+{
+    if (!out && n_samples) { set_error("ga_synth_fill_host: NULL output"); return GA_ERR_ARG; }
+    for (uint32_t i = 0; i < n_samples; i++) out[i] = synth::sample(seed, group, relay, first + i, utt_samples);
+    return GA_OK;
+}
+
+extern "C" int ga_synth_fill_batch_host(void *pcm, uint64_t seed, uint32_t group_base, uint32_t n_streams,
+                                        uint32_t group_size, uint32_t n_msgs, uint32_t msg_samples,
+                                        uint32_t n_threads)
+{
+    if (!pcm || group_size == 0) { set_error("ga_synth_fill_batch_host: bad argument"); return GA_ERR_ARG; }
+    if (n_threads == 0) n_threads = 1;
+    int16_t *out = static_cast<int16_t *>(pcm);
+    const uint32_t utt = n_msgs * msg_samples;
+    std::atomic<uint32_t> next{0};
+    auto work = [&]() {
+        for (;;) {
+            const uint32_t s = next.fetch_add(1);
+            if (s >= n_streams) break;
+            for (uint32_t m = 0; m < n_msgs; m++) {
+                int16_t *dst = out + (static_cast<uint64_t>(m) * n_streams + s) * msg_samples;
+                for (uint32_t k = 0; k < msg_samples; k++)
+                    dst[k] = synth::sample(seed, group_base + s / group_size, s % group_size, m * msg_samples + k, utt);
+            }
+        }
+    };
+    std::vector<std::thread> th;
+    for (uint32_t i = 1; i < n_threads; i++) th.emplace_back(work);
+    work();
+    for (auto &t : th) t.join();
+    return GA_OK;
+}
+
+__global__ void synth_batch_kernel(int16_t *pcm, uint64_t seed, uint32_t group_base, uint32_t n_streams,
+                                   uint32_t group_size, uint32_t n_msgs, uint32_t msg_samples)
+{
+    const uint64_t total = static_cast<uint64_t>(n_msgs) * n_streams * msg_samples;
+    const uint32_t utt = n_msgs * msg_samples;
+    for (uint64_t i = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<uint64_t>(gridDim.x) * blockDim.x) {
+        const uint32_t k = static_cast<uint32_t>(i % msg_samples);
+        const uint64_t ms = i / msg_samples;
+        const uint32_t s = static_cast<uint32_t>(ms % n_streams);
+        const uint32_t m = static_cast<uint32_t>(ms / n_streams);
+        pcm[i] = synth::sample(seed, group_base + s / group_size, s % group_size, m * msg_samples + k, utt);
+    }
+}
+
+__global__ void synth_batch_map_kernel(int16_t *pcm, uint64_t seed, const uint32_t *__restrict__ group,
+                                       const uint32_t *__restrict__ relay, uint32_t n_streams,
+                                       uint32_t n_msgs, uint32_t msg_samples)
+{
+    const uint64_t total = static_cast<uint64_t>(n_msgs) * n_streams * msg_samples;
+    const uint32_t utt = n_msgs * msg_samples;
+    for (uint64_t i = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<uint64_t>(gridDim.x) * blockDim.x) {
+        const uint32_t k = static_cast<uint32_t>(i % msg_samples);
+        const uint64_t ms = i / msg_samples;
+        const uint32_t s = static_cast<uint32_t>(ms % n_streams);
+        const uint32_t m = static_cast<uint32_t>(ms / n_streams);
+        pcm[i] = synth::sample(seed, group[s], relay[s], m * msg_samples + k, utt);
+    }
+}
+
+extern "C" int ga_synth_fill_batch_device_map(void *d_pcm, uint64_t seed, const uint32_t *d_group,
+                                              const uint32_t *d_relay, uint32_t n_streams,
+                                              uint32_t n_msgs, uint32_t msg_samples, void *stream)
+{
+    if (!d_pcm || !d_group || !d_relay) { set_error("ga_synth_fill_batch_device_map: bad argument"); return GA_ERR_ARG; }
+    const uint64_t total = static_cast<uint64_t>(n_msgs) * n_streams * msg_samples;
+    if (total == 0) return GA_OK;
+    int sms = 0;
+    int rc = num_sms(&sms);
+    if (rc) return rc;
+    synth_batch_map_kernel<<<sms * 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<int16_t *>(d_pcm), seed, d_group, d_relay, n_streams, n_msgs, msg_samples);
+    GA_CHECK_LAUNCH("synth_batch_map_kernel");
+    return GA_OK;
+}
+
+extern "C" int ga_synth_fill_batch_device(void *d_pcm, uint64_t seed, uint32_t group_base,
+                                          uint32_t n_streams, uint32_t group_size, uint32_t n_msgs,
+                                          uint32_t msg_samples, void *stream)
+{
+    if (!d_pcm || group_size == 0) { set_error("ga_synth_fill_batch_device: bad argument"); return GA_ERR_ARG; }
+    const uint64_t total = static_cast<uint64_t>(n_msgs) * n_streams * msg_samples;
+    if (total == 0) return GA_OK;
+    int sms = 0;
+    int rc = num_sms(&sms);
+    if (rc) return rc;
+    synth_batch_kernel<<<sms * 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<int16_t *>(d_pcm), seed, group_base, n_streams, group_size, n_msgs, msg_samples);
+    GA_CHECK_LAUNCH("synth_batch_kernel");
+    return GA_OK;
+}

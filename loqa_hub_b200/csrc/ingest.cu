@@ -1,0 +1,383 @@
+// ingest.cu — fused relay-message ingest for B200 (sm_100a).
+//
+// Replaces, for a whole batch of relay messages per launch, the reference's per-chunk
+// scalar loops (paths relative to the loqa-hub tree):
+//   bytesToFloat32Array          internal/grpc/audio_service.go:1048-1101   (convert + side stats)
+//   calculateSignalStrength      internal/grpc/audio_service.go:818-852     (sumsq / rms / nonzero / peak)
+//   voice-event audio fingerprint (README.md:50, API.md:170; hook events/voice_event.go:84-88)
+//
+// Work decomposition.  A warp owns a tile of 32 consecutive messages and streams them
+// through shared memory in CH-byte slices per message ("rows"): every lane issues one
+// TMA bulk copy (cp.async.bulk -> UBLKCP) for its own row into a STAGES-deep ring of
+// stage buffers, completion is tracked by one mbarrier per stage.  Each slice is then
+// consumed twice from shared memory:
+//   phase A (warp-cooperative, coalesced): 4 samples per lane -> one 16-byte streaming
+//           store of f32 samples; two rows per warp instruction, 256 B contiguous each;
+//   phase B (lane = message): the lane walks ITS message's 64-byte blocks: the SHA-256
+//           compression (schedule in registers) and the reference's strictly sequential
+//           float64 sum of float32 squares, so sumsq/rms are bit-identical to the Go loop.
+// Rows are padded by 16 B so the lane-per-row LDS.128 pattern is bank-conflict free.
+// The integer ALU pipe (SHA-256, ~22 instructions per byte) bounds the fused kernel; the
+// convert/feature-only instantiation is HBM-bound.  No tensor cores: nothing here is a
+// contraction.
+#include "common.cuh"
+#include "sha256.cuh"
+
+namespace ga {
+
+constexpr int kWarpsPerBlock = 4;
+
+template <int CH, int STAGES>
+struct TileSmem {
+    static constexpr int kRowStride = CH + 16;          // (CH/16 + 1) is odd -> conflict-free LDS.128
+    static constexpr int kStageBytes = 32 * kRowStride;
+    static constexpr int kWarpBytes = STAGES * kStageBytes + 128;   // + barriers (padded)
+    static_assert(CH % 64 == 0, "slices must hold whole SHA-256 blocks");
+    static_assert(((CH / 16) + 1) % 2 == 1, "row stride must be an odd number of 16-byte units");
+};
+
+struct IngestParams {
+    const uint8_t *pcm;
+    const ga_desc *desc;
+    float *samples;
+    ga_result *results;
+    ga_frame *frames;
+    double vad;
+    uint32_t n_msgs;
+    uint32_t n_tiles;
+};
+
+// Running statistics for one span of samples, in the reference's arithmetic.
+struct Feat {
+    double sum;      // Σ float64(float32(s*s)), index order
+    uint32_t n;
+    uint32_t nz;
+    int amax;        // max |int16| — peak = |amax / 32767| because the conversion is monotonic
+    __device__ __forceinline__ void reset() { sum = 0.0; n = 0; nz = 0; amax = 0; }
+    __device__ __forceinline__ void add(int v)
+    {
+        float s = pcm_to_f32(v);
+        sum += sq_f64(s);
+        nz += (v != 0);
+        amax = max(amax, abs(v));
+    }
+    __device__ __forceinline__ float peak() const { return pcm_to_f32(amax); }
+    __device__ __forceinline__ double rms() const
+    {
+        return n ? __dsqrt_rn(__ddiv_rn(sum, static_cast<double>(n))) : 0.0;
+    }
+};
+
+__device__ __forceinline__ int s16_lo(uint32_t w) { return static_cast<int>(static_cast<int16_t>(w & 0xffffu)); }
+__device__ __forceinline__ int s16_hi(uint32_t w) { return static_cast<int>(w) >> 16; }
+
+template <int CH, int STAGES, uint32_t MODE>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+ingest_kernel(const IngestParams p)
+{
+    using L = TileSmem<CH, STAGES>;
+    constexpr bool kConvert = (MODE & GA_DO_CONVERT) != 0;
+    constexpr bool kFeat = (MODE & GA_DO_FEATURES) != 0;
+    constexpr bool kSha = (MODE & GA_DO_SHA256) != 0;
+    constexpr uint32_t FULL = 0xffffffffu;
+
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint8_t *wbase = smem + warp * L::kWarpBytes;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(wbase + STAGES * L::kStageBytes);
+
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; s++) mbar_init(&bars[s], 1);
+        fence_mbar_init();
+    }
+    __syncwarp();
+
+    const uint32_t gw = blockIdx.x * kWarpsPerBlock + warp;
+    const uint32_t nw = gridDim.x * kWarpsPerBlock;
+
+    // ------------------------------------------------------------ producer cursor
+    uint32_t p_tile = gw, p_chunk = 0, p_nch = 0, p_nb = 0;
+    uint64_t p_in = 0;
+    auto p_load = [&]() {
+        p_nb = 0; p_in = 0; p_nch = 0;
+        if (p_tile < p.n_tiles) {
+            uint32_t i = p_tile * 32 + lane;
+            uint32_t nch = 0;
+            if (i < p.n_msgs) {
+                p_in = p.desc[i].in_off;
+                p_nb = p.desc[i].nbytes;
+                nch = p_nb ? (p_nb - 1) / CH + 1 : 1;
+            }
+            p_nch = __reduce_max_sync(FULL, nch);
+        }
+    };
+    auto produce = [&](int stage) {
+        if (p_tile >= p.n_tiles) return;                       // warp-uniform
+        const uint32_t lo = p_chunk * CH;
+        uint32_t bytes = p_nb > lo ? min(p_nb - lo, static_cast<uint32_t>(CH)) : 0u;
+        bytes = (bytes + 15u) & ~15u;
+        const uint32_t total = __reduce_add_sync(FULL, bytes);
+        if (lane == 0) mbar_arrive_expect_tx(&bars[stage], total);
+        __syncwarp();
+        if (bytes)
+            bulk_g2s(wbase + stage * L::kStageBytes + lane * L::kRowStride, p.pcm + p_in + lo,
+                     bytes, &bars[stage]);
+        if (++p_chunk == p_nch) {
+            p_tile += nw;
+            p_chunk = 0;
+            p_load();
+        }
+    };
+
+    p_load();
+#pragma unroll
+    for (int s = 0; s < STAGES; s++) produce(s);
+
+    // ------------------------------------------------------------ consumer
+    uint32_t it = 0;   // stage jobs consumed so far by this warp
+    for (uint32_t c_tile = gw; c_tile < p.n_tiles; c_tile += nw) {
+        const uint32_t mi = c_tile * 32 + lane;
+        const bool valid = mi < p.n_msgs;
+        uint32_t nb = 0, flags = 0, frame_off = 0;
+        uint64_t out_off = 0;
+        if (valid) {
+            const ga_desc d = p.desc[mi];
+            nb = d.nbytes; flags = d.flags; frame_off = d.frame_off; out_off = d.out_off;
+        }
+        const uint32_t my_nch = valid ? (nb ? (nb - 1) / CH + 1 : 1) : 0;
+        const uint32_t c_nch = __reduce_max_sync(FULL, my_nch);
+        const uint32_t nb_even = nb & ~1u;
+
+        Sha256State sha;
+        if (kSha) sha.init();
+        Feat msg, frm;
+        msg.reset(); frm.reset();
+        uint32_t fidx = 0;
+
+        auto emit_frame = [&]() {
+            if (p.frames) {
+                ga_frame f;
+                f.sumsq = frm.sum; f.rms = frm.rms(); f.n_samples = frm.n; f.nonzero = frm.nz;
+                f.peak = frm.peak(); f.vad = f.rms > p.vad ? 1u : 0u;
+                p.frames[static_cast<uint64_t>(frame_off) + fidx] = f;
+            }
+            fidx++;
+            frm.reset();
+        };
+        // one sample in reference order: message-level and frame-level chains
+        auto feat_sample = [&](int v) {
+            float s = pcm_to_f32(v);
+            double q = sq_f64(s);
+            msg.sum += q; frm.sum += q;
+            uint32_t z = (v != 0);
+            msg.nz += z; frm.nz += z;
+            int a = abs(v);
+            msg.amax = max(msg.amax, a); frm.amax = max(frm.amax, a);
+        };
+
+        for (uint32_t c = 0; c < c_nch; c++, it++) {
+            const int stage = it % STAGES;
+            const uint32_t parity = (it / STAGES) & 1u;
+            const uint8_t *sbase = wbase + stage * L::kStageBytes;
+            const uint32_t lo = c * CH;
+            mbar_wait(&bars[stage], parity);
+
+            // ---------------- phase A: cooperative convert + coalesced store
+            if (kConvert) {
+                constexpr int VPR = CH / 8;   // 4-sample vectors per row slice
+#pragma unroll 4
+                for (int k = 0; k < VPR; k++) {
+                    const int v = k * 32 + lane;
+                    const int row = v / VPR, col = v % VPR;
+                    const uint32_t r_even = __shfl_sync(FULL, nb_even, row);
+                    const uint64_t r_out = __shfl_sync(FULL, out_off, row);
+                    const uint32_t byte0 = lo + col * 8;
+                    if (byte0 < r_even) {
+                        const uint2 raw = *reinterpret_cast<const uint2 *>(sbase + row * L::kRowStride + col * 8);
+                        const float f0 = pcm_to_f32(s16_lo(raw.x)), f1 = pcm_to_f32(s16_hi(raw.x));
+                        const float f2 = pcm_to_f32(s16_lo(raw.y)), f3 = pcm_to_f32(s16_hi(raw.y));
+                        float *dst = p.samples + r_out + (byte0 >> 1);
+                        const uint32_t nvalid = (r_even - byte0) >> 1;
+                        if (nvalid >= 4 && (r_out & 3ull) == 0) {
+                            st_global_v4(dst, f0, f1, f2, f3);
+                        } else {
+                            dst[0] = f0;
+                            if (nvalid > 1) dst[1] = f1;
+                            if (nvalid > 2) dst[2] = f2;
+                            if (nvalid > 3) dst[3] = f3;
+                        }
+                    }
+                }
+            }
+
+            // ---------------- phase B: lane = message
+            if ((kFeat || kSha) && c < my_nch) {
+                const uint8_t *rowp = sbase + lane * L::kRowStride;
+                const uint32_t hi = min(nb, lo + CH);
+                const uint32_t span = hi - lo;
+                const uint32_t nfull = span >> 6;
+                for (uint32_t b = 0; b < nfull; b++) {
+                    uint32_t w[16];
+                    const uint4 *q = reinterpret_cast<const uint4 *>(rowp + b * 64);
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const uint4 t = q[j];
+                        w[4 * j] = t.x; w[4 * j + 1] = t.y; w[4 * j + 2] = t.z; w[4 * j + 3] = t.w;
+                    }
+                    if (kFeat) {
+#pragma unroll
+                        for (int j = 0; j < 16; j++) { feat_sample(s16_lo(w[j])); feat_sample(s16_hi(w[j])); }
+                        msg.n += 32; frm.n += 32;
+                        if (frm.n == GA_FRAME_SAMPLES) emit_frame();
+                    }
+                    if (kSha) {
+#pragma unroll
+                        for (int j = 0; j < 16; j++) w[j] = bswap32(w[j]);
+                        sha256_compress(sha, w);
+                    }
+                }
+                if (c == my_nch - 1) {
+                    // the message ends in this slice: tail samples, padding block(s)
+                    const uint32_t rem = span & 63u;
+                    uint32_t w[16];
+#pragma unroll
+                    for (int j = 0; j < 16; j++) w[j] = 0;
+                    if (rem) {
+                        const uint4 *q = reinterpret_cast<const uint4 *>(rowp + nfull * 64);
+#pragma unroll
+                        for (int j = 0; j < 4; j++) {
+                            const uint4 t = q[j];
+                            w[4 * j] = t.x; w[4 * j + 1] = t.y; w[4 * j + 2] = t.z; w[4 * j + 3] = t.w;
+                        }
+                    }
+                    if (kFeat) {
+                        const uint32_t ns = rem >> 1;    // an odd trailing byte is not a sample
+#pragma unroll
+                        for (int j = 0; j < 16; j++) {
+                            if (2u * j < ns) feat_sample(s16_lo(w[j]));
+                            if (2u * j + 1 < ns) feat_sample(s16_hi(w[j]));
+                        }
+                        msg.n += ns; frm.n += ns;
+                        if (frm.n) emit_frame();
+                    }
+                    if (kSha) {
+                        // zero everything at and beyond byte `rem`, then append 0x80
+#pragma unroll
+                        for (int j = 0; j < 16; j++) {
+                            const uint32_t b0 = 4u * j;
+                            uint32_t m = 0;
+                            if (b0 + 4 <= rem) m = 0xffffffffu;
+                            else if (b0 < rem) m = (1u << (8 * (rem - b0))) - 1u;
+                            uint32_t x = w[j] & m;
+                            if ((rem >> 2) == static_cast<uint32_t>(j)) x |= 0x80u << (8 * (rem & 3u));
+                            w[j] = bswap32(x);
+                        }
+                        const uint64_t bits = static_cast<uint64_t>(nb) * 8ull;
+                        if (rem >= 56) {
+                            sha256_compress(sha, w);
+#pragma unroll
+                            for (int j = 0; j < 16; j++) w[j] = 0;
+                        }
+                        w[14] = static_cast<uint32_t>(bits >> 32);
+                        w[15] = static_cast<uint32_t>(bits);
+                        sha256_compress(sha, w);
+                    }
+                }
+            }
+
+            __syncwarp();          // every lane is done reading this stage
+            produce(stage);        // refill it with the slice STAGES jobs ahead
+        }
+
+        // ---------------- result record
+        if (valid) {
+            uint4 *r = reinterpret_cast<uint4 *>(p.results + mi);
+            if (kSha) {
+                r[0] = make_uint4(bswap32(sha.h[0]), bswap32(sha.h[1]), bswap32(sha.h[2]), bswap32(sha.h[3]));
+                r[1] = make_uint4(bswap32(sha.h[4]), bswap32(sha.h[5]), bswap32(sha.h[6]), bswap32(sha.h[7]));
+            } else {
+                r[0] = make_uint4(0, 0, 0, 0);
+                r[1] = make_uint4(0, 0, 0, 0);
+            }
+            double sumsq = 0.0, rms = 0.0;
+            uint32_t nzc = 0, fl = flags << 8;
+            float pk = 0.0f;
+            if (kFeat) {
+                sumsq = msg.sum; rms = msg.rms(); nzc = msg.nz; pk = msg.peak();
+                if (rms > p.vad) fl |= 1u;
+            }
+            r[2] = make_uint4(__double2loint(sumsq), __double2hiint(sumsq), __double2loint(rms), __double2hiint(rms));
+            r[3] = make_uint4(nb >> 1, nzc, __float_as_uint(pk), fl);
+        }
+    }
+}
+
+// ---------------------------------------------------------------- host launcher
+template <int CH, int STAGES, uint32_t MODE>
+static int launch_ingest(const IngestParams &p, cudaStream_t st)
+{
+    using L = TileSmem<CH, STAGES>;
+    constexpr int smem = kWarpsPerBlock * L::kWarpBytes;
+    auto kern = ingest_kernel<CH, STAGES, MODE>;
+    static thread_local int configured_dev = -1;
+    static thread_local int blocks_per_sm = 0;
+    int dev = 0;
+    GA_CUDA_TRY(cudaGetDevice(&dev));
+    if (configured_dev != dev) {
+        GA_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        GA_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern,
+                                                                  kWarpsPerBlock * 32, smem));
+        if (blocks_per_sm < 1) blocks_per_sm = 1;
+        configured_dev = dev;
+    }
+    int sms = 0;
+    int rc = num_sms(&sms);
+    if (rc) return rc;
+    uint32_t want = (p.n_tiles + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    uint32_t grid = static_cast<uint32_t>(sms * blocks_per_sm);
+    if (grid > want) grid = want;
+    if (grid == 0) return GA_OK;
+    kern<<<grid, kWarpsPerBlock * 32, smem, st>>>(p);
+    GA_CHECK_LAUNCH("ingest_kernel");
+    return GA_OK;
+}
+
+}  // namespace ga
+
+extern "C" int ga_k_ingest(const void *d_pcm, const ga_desc *d_desc, uint32_t n_msgs,
+                           float *d_samples, ga_result *d_results, ga_frame *d_frames,
+                           uint32_t mode, double vad_threshold, void *stream)
+{
+    using namespace ga;
+    if (n_msgs == 0) return GA_OK;
+    if (!d_pcm || !d_desc || !d_results) { set_error("ga_k_ingest: NULL pcm/desc/results"); return GA_ERR_ARG; }
+    mode &= GA_DO_ALL;
+    if (mode == 0) { set_error("ga_k_ingest: empty mode"); return GA_ERR_ARG; }
+    if ((mode & GA_DO_CONVERT) && !d_samples) { set_error("ga_k_ingest: GA_DO_CONVERT needs d_samples"); return GA_ERR_ARG; }
+    if ((reinterpret_cast<uintptr_t>(d_pcm) & 15u) || (reinterpret_cast<uintptr_t>(d_samples) & 15u) ||
+        (reinterpret_cast<uintptr_t>(d_results) & 15u) || (reinterpret_cast<uintptr_t>(d_desc) & 15u)) {
+        set_error("ga_k_ingest: device pointers must be 16-byte aligned");
+        return GA_ERR_ARG;
+    }
+    IngestParams p;
+    p.pcm = static_cast<const uint8_t *>(d_pcm);
+    p.desc = d_desc;
+    p.samples = d_samples;
+    p.results = d_results;
+    p.frames = d_frames;
+    p.vad = vad_threshold;
+    p.n_msgs = n_msgs;
+    p.n_tiles = (n_msgs + 31) / 32;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    constexpr int CH = 128, ST = 3;
+    switch (mode) {
+        case 1: return launch_ingest<CH, ST, 1>(p, st);
+        case 2: return launch_ingest<CH, ST, 2>(p, st);
+        case 3: return launch_ingest<CH, ST, 3>(p, st);
+        case 4: return launch_ingest<CH, ST, 4>(p, st);
+        case 5: return launch_ingest<CH, ST, 5>(p, st);
+        case 6: return launch_ingest<CH, ST, 6>(p, st);
+        default: return launch_ingest<CH, ST, 7>(p, st);
+    }
+}
