@@ -207,6 +207,11 @@ int ga_ticket_frames(ga_ctx *ctx, uint64_t ticket, uint32_t *n_frames);
 int ga_fetch_samples(ga_ctx *ctx, uint32_t stream_id, uint64_t first, uint64_t n, float *out);
 int ga_stream_info(ga_ctx *ctx, uint32_t stream_id, uint64_t *n_samples, uint64_t *wake_samples);
 int ga_stream_reset(ga_ctx *ctx, uint32_t stream_id);
+/* Device address of the f32 sample arena (stream s starts at s * arena_samples; its wake-word
+ * region first, its speech region at + wake_samples_max).  For harnesses that run the
+ * ga_k_* arbitration sequence (e.g. with an exchange step between shards) on the context's
+ * samples.  Valid until ga_shutdown; wait all tickets before reading. */
+int ga_device_arena(ga_ctx *ctx, void **d_arena);
 
 /* performArbitration for many windows (audio_service.go:505-571).  Host arrays:
  * seg_offsets[n_windows+1], stream_ids / status_in / scores / status_out per member,

@@ -58,6 +58,7 @@ SYMBOLS = {
     "ga_fetch_samples": (_i32, [_vp, _u32, _u64, _u64, _vp]),
     "ga_stream_info": (_i32, [_vp, _u32, C.POINTER(_u64), C.POINTER(_u64)]),
     "ga_stream_reset": (_i32, [_vp, _u32]),
+    "ga_device_arena": (_i32, [_vp, C.POINTER(_vp)]),
     "ga_arbitrate": (_i32, [_vp, _vp, _u32, _vp, _vp, _vp, _vp, _vp]),
     "ga_bytes_to_float32": (_i32, [_vp, _vp, _sz, _vp, C.POINTER(_sz), _vp]),
     "ga_signal_strength": (_i32, [_vp, _vp, _sz, C.POINTER(C.c_double), _vp]),

@@ -414,6 +414,14 @@ extern "C" int ga_stream_reset(ga_ctx *ctx, uint32_t stream_id)
     return GA_OK;
 }
 
+extern "C" int ga_device_arena(ga_ctx *ctx, void **d_arena)
+{
+    if (!ctx || !d_arena) { set_error("ga_device_arena: NULL argument"); return GA_ERR_ARG; }
+    if (!ctx->d_arena) { set_error("ga_device_arena: context does not materialise samples"); return GA_ERR_STATE; }
+    *d_arena = ctx->d_arena;
+    return GA_OK;
+}
+
 extern "C" int ga_fetch_samples(ga_ctx *ctx, uint32_t stream_id, uint64_t first, uint64_t n, float *out)
 {
     if (!ctx || stream_id >= ctx->cfg.max_streams || (n && !out)) { set_error("ga_fetch_samples: bad argument"); return GA_ERR_ARG; }

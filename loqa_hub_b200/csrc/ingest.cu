@@ -20,6 +20,8 @@
 // The integer ALU pipe (SHA-256, ~22 instructions per byte) bounds the fused kernel; the
 // convert/feature-only instantiation is HBM-bound.  No tensor cores: nothing here is a
 // contraction.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "sha256.cuh"
 
@@ -47,32 +49,46 @@ struct IngestParams {
     uint32_t n_tiles;
 };
 
-// Running statistics for one span of samples, in the reference's arithmetic.
-struct Feat {
-    double sum;      // Σ float64(float32(s*s)), index order
+// Two int16 samples -> two exact floats without the conversion (XU) pipe: bias each half
+// by 0x8000, splice it under the exponent of 2^23 and subtract 2^23 + 32768.
+__device__ __forceinline__ void unpack2(uint32_t w, float &lo, float &hi)
+{
+    const uint32_t x = w ^ 0x80008000u;
+    lo = __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7610)) - 8421376.0f;
+    hi = __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7632)) - 8421376.0f;
+}
+
+// Statistics of one span of samples in the reference's arithmetic.  `sum` is the strictly
+// sequential float64 chain; the order-independent pieces are kept packed: max/min of both
+// int16 halves in one VIMNMX.S16x2 each, non-zero counts as two 16-bit counters.
+struct Span {
+    double sum;
     uint32_t n;
-    uint32_t nz;
-    int amax;        // max |int16| — peak = |amax / 32767| because the conversion is monotonic
-    __device__ __forceinline__ void reset() { sum = 0.0; n = 0; nz = 0; amax = 0; }
-    __device__ __forceinline__ void add(int v)
+    uint32_t mx, mn;     // packed running max / min of the raw int16 halves
+    uint32_t nzp;        // packed non-zero counters (flush before 65,535 samples per half)
+    __device__ __forceinline__ void reset() { sum = 0.0; n = 0; mx = 0x80008000u; mn = 0x7FFF7FFFu; nzp = 0; }
+    __device__ __forceinline__ void stats_word(uint32_t w)
     {
-        float s = pcm_to_f32(v);
-        sum += sq_f64(s);
-        nz += (v != 0);
-        amax = max(amax, abs(v));
+        mx = __vmaxs2(mx, w);
+        mn = __vmins2(mn, w);
+        const uint32_t t = (w & 0x7FFF7FFFu) + 0x7FFF7FFFu;      // bit 15/31 set iff the half is non-zero
+        nzp += ((t | w) & 0x80008000u) >> 15;
     }
-    __device__ __forceinline__ float peak() const { return pcm_to_f32(amax); }
-    __device__ __forceinline__ double rms() const
+    __device__ __forceinline__ uint32_t nonzero() const { return (nzp & 0xFFFFu) + (nzp >> 16); }
+    // max |v| = max(|max v|, |min v|) per half.  Written with abs(), not max(a, -b): nvcc 12.9
+    // fuses the latter into VIMNMX3.RELU and drops the negation (observed on sm_100a; see
+    // tools/dbg_vmin.cu and tests/test_gpu_ingest.py::test_peak_of_negative_samples_in_either_half).
+    __device__ __forceinline__ int amax() const
     {
-        return n ? __dsqrt_rn(__ddiv_rn(sum, static_cast<double>(n))) : 0.0;
+        const int a = abs(static_cast<int>(mx) >> 16), b = abs(static_cast<int>(mn) >> 16);
+        const int c = abs(static_cast<int>(static_cast<int16_t>(mx & 0xFFFFu)));
+        const int d = abs(static_cast<int>(static_cast<int16_t>(mn & 0xFFFFu)));
+        return max(max(a, b), max(c, d));
     }
 };
 
-__device__ __forceinline__ int s16_lo(uint32_t w) { return static_cast<int>(static_cast<int16_t>(w & 0xffffu)); }
-__device__ __forceinline__ int s16_hi(uint32_t w) { return static_cast<int>(w) >> 16; }
-
-template <int CH, int STAGES, uint32_t MODE>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+template <int CH, int STAGES, uint32_t MODE, int MINB>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, MINB)
 ingest_kernel(const IngestParams p)
 {
     using L = TileSmem<CH, STAGES>;
@@ -151,29 +167,35 @@ ingest_kernel(const IngestParams p)
 
         Sha256State sha;
         if (kSha) sha.init();
-        Feat msg, frm;
-        msg.reset(); frm.reset();
-        uint32_t fidx = 0;
+        // message-level: the f64 chain runs over the whole message; counts / extrema are
+        // merged from the frames (they do not depend on order)
+        double msg_sum = 0.0;
+        uint32_t msg_nz = 0, fidx = 0;
+        int msg_amax = 0;
+        Span frm;
+        frm.reset();
 
         auto emit_frame = [&]() {
+            const uint32_t fnz = frm.nonzero();
+            const int fa = frm.amax();
             if (p.frames) {
                 ga_frame f;
-                f.sumsq = frm.sum; f.rms = frm.rms(); f.n_samples = frm.n; f.nonzero = frm.nz;
-                f.peak = frm.peak(); f.vad = f.rms > p.vad ? 1u : 0u;
+                f.sumsq = frm.sum;
+                f.rms = __dsqrt_rn(__ddiv_rn(frm.sum, static_cast<double>(frm.n)));
+                f.n_samples = frm.n; f.nonzero = fnz;
+                f.peak = pcm_to_f32(fa); f.vad = f.rms > p.vad ? 1u : 0u;
                 p.frames[static_cast<uint64_t>(frame_off) + fidx] = f;
             }
+            msg_nz += fnz;
+            msg_amax = max(msg_amax, fa);
             fidx++;
             frm.reset();
         };
-        // one sample in reference order: message-level and frame-level chains
-        auto feat_sample = [&](int v) {
-            float s = pcm_to_f32(v);
-            double q = sq_f64(s);
-            msg.sum += q; frm.sum += q;
-            uint32_t z = (v != 0);
-            msg.nz += z; frm.nz += z;
-            int a = abs(v);
-            msg.amax = max(msg.amax, a); frm.amax = max(frm.amax, a);
+        // one sample, already exact as a float, in reference order (audio_service.go:827-828)
+        auto chain = [&](float v) {
+            const double q = sq_f64(pcm_to_f32(v));
+            msg_sum += q;
+            frm.sum += q;
         };
 
         for (uint32_t c = 0; c < c_nch; c++, it++) {
@@ -195,8 +217,11 @@ ingest_kernel(const IngestParams p)
                     const uint32_t byte0 = lo + col * 8;
                     if (byte0 < r_even) {
                         const uint2 raw = *reinterpret_cast<const uint2 *>(sbase + row * L::kRowStride + col * 8);
-                        const float f0 = pcm_to_f32(s16_lo(raw.x)), f1 = pcm_to_f32(s16_hi(raw.x));
-                        const float f2 = pcm_to_f32(s16_lo(raw.y)), f3 = pcm_to_f32(s16_hi(raw.y));
+                        float v0, v1, v2, v3;
+                        unpack2(raw.x, v0, v1);
+                        unpack2(raw.y, v2, v3);
+                        const float f0 = pcm_to_f32(v0), f1 = pcm_to_f32(v1);
+                        const float f2 = pcm_to_f32(v2), f3 = pcm_to_f32(v3);
                         float *dst = p.samples + r_out + (byte0 >> 1);
                         const uint32_t nvalid = (r_even - byte0) >> 1;
                         if (nvalid >= 4 && (r_out & 3ull) == 0) {
@@ -211,79 +236,81 @@ ingest_kernel(const IngestParams p)
                 }
             }
 
-            // ---------------- phase B: lane = message
+            // ---------------- phase B: lane = message.  One loop over the 64-byte blocks this
+            // slice contributes, including the padding block(s) when the message ends here, so
+            // the unrolled compression exists once in the instruction stream.
             if ((kFeat || kSha) && c < my_nch) {
                 const uint8_t *rowp = sbase + lane * L::kRowStride;
-                const uint32_t hi = min(nb, lo + CH);
-                const uint32_t span = hi - lo;
+                const uint32_t span = min(nb, lo + CH) - lo;
                 const uint32_t nfull = span >> 6;
-                for (uint32_t b = 0; b < nfull; b++) {
+                const uint32_t rem = span & 63u;
+                const bool last = (c == my_nch - 1);
+                const uint32_t nblk = nfull + (last ? (kSha ? (rem >= 56 ? 2u : 1u) : (rem ? 1u : 0u)) : 0u);
+                for (uint32_t b = 0; b < nblk; b++) {
+                    const uint32_t vb = b < nfull ? 64u : (b == nfull ? rem : 0u);   // data bytes in this block
                     uint32_t w[16];
-                    const uint4 *q = reinterpret_cast<const uint4 *>(rowp + b * 64);
-#pragma unroll
-                    for (int j = 0; j < 4; j++) {
-                        const uint4 t = q[j];
-                        w[4 * j] = t.x; w[4 * j + 1] = t.y; w[4 * j + 2] = t.z; w[4 * j + 3] = t.w;
-                    }
-                    if (kFeat) {
-#pragma unroll
-                        for (int j = 0; j < 16; j++) { feat_sample(s16_lo(w[j])); feat_sample(s16_hi(w[j])); }
-                        msg.n += 32; frm.n += 32;
-                        if (frm.n == GA_FRAME_SAMPLES) emit_frame();
-                    }
-                    if (kSha) {
-#pragma unroll
-                        for (int j = 0; j < 16; j++) w[j] = bswap32(w[j]);
-                        sha256_compress(sha, w);
-                    }
-                }
-                if (c == my_nch - 1) {
-                    // the message ends in this slice: tail samples, padding block(s)
-                    const uint32_t rem = span & 63u;
-                    uint32_t w[16];
-#pragma unroll
-                    for (int j = 0; j < 16; j++) w[j] = 0;
-                    if (rem) {
-                        const uint4 *q = reinterpret_cast<const uint4 *>(rowp + nfull * 64);
+                    if (vb) {
+                        const uint4 *q = reinterpret_cast<const uint4 *>(rowp + b * 64);
 #pragma unroll
                         for (int j = 0; j < 4; j++) {
                             const uint4 t = q[j];
                             w[4 * j] = t.x; w[4 * j + 1] = t.y; w[4 * j + 2] = t.z; w[4 * j + 3] = t.w;
                         }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 16; j++) w[j] = 0;
                     }
                     if (kFeat) {
-                        const uint32_t ns = rem >> 1;    // an odd trailing byte is not a sample
+                        if (vb == 64) {
 #pragma unroll
-                        for (int j = 0; j < 16; j++) {
-                            if (2u * j < ns) feat_sample(s16_lo(w[j]));
-                            if (2u * j + 1 < ns) feat_sample(s16_hi(w[j]));
+                            for (int j = 0; j < 16; j++) {
+                                float a, bb;
+                                unpack2(w[j], a, bb);
+                                chain(a);
+                                chain(bb);
+                                frm.stats_word(w[j]);
+                            }
+                            frm.n += 32;
+                            if (frm.n == GA_FRAME_SAMPLES) emit_frame();
+                        } else if (vb >= 2) {
+                            // tail of the message: fewer than 32 samples, rolled loop from shared memory
+                            const uint32_t ns = vb >> 1;           // an odd trailing byte is not a sample
+                            const uint16_t *hp = reinterpret_cast<const uint16_t *>(rowp + b * 64);
+                            for (uint32_t k = 0; k < ns; k++) {
+                                const uint32_t h = hp[k];
+                                float a, bb;
+                                unpack2(h, a, bb);
+                                chain(a);
+                                frm.stats_word(h);                  // upper half is a zero sample: neutral
+                            }
+                            frm.n += ns;
                         }
-                        msg.n += ns; frm.n += ns;
-                        if (frm.n) emit_frame();
                     }
                     if (kSha) {
-                        // zero everything at and beyond byte `rem`, then append 0x80
+                        if (vb < 64) {
+                            // zero everything at and beyond byte vb; append 0x80 right after the data
 #pragma unroll
-                        for (int j = 0; j < 16; j++) {
-                            const uint32_t b0 = 4u * j;
-                            uint32_t m = 0;
-                            if (b0 + 4 <= rem) m = 0xffffffffu;
-                            else if (b0 < rem) m = (1u << (8 * (rem - b0))) - 1u;
-                            uint32_t x = w[j] & m;
-                            if ((rem >> 2) == static_cast<uint32_t>(j)) x |= 0x80u << (8 * (rem & 3u));
-                            w[j] = bswap32(x);
+                            for (int j = 0; j < 16; j++) {
+                                const uint32_t b0 = 4u * j;
+                                uint32_t m = 0;
+                                if (b0 + 4 <= vb) m = 0xffffffffu;
+                                else if (b0 < vb) m = (1u << (8 * (vb - b0))) - 1u;
+                                uint32_t x = w[j] & m;
+                                if (b == nfull && (vb >> 2) == static_cast<uint32_t>(j)) x |= 0x80u << (8 * (vb & 3u));
+                                w[j] = x;
+                            }
                         }
-                        const uint64_t bits = static_cast<uint64_t>(nb) * 8ull;
-                        if (rem >= 56) {
-                            sha256_compress(sha, w);
 #pragma unroll
-                            for (int j = 0; j < 16; j++) w[j] = 0;
+                        for (int j = 0; j < 16; j++) w[j] = bswap32(w[j]);
+                        if (last && b == nblk - 1) {
+                            const uint64_t bits = static_cast<uint64_t>(nb) * 8ull;
+                            w[14] = static_cast<uint32_t>(bits >> 32);
+                            w[15] = static_cast<uint32_t>(bits);
                         }
-                        w[14] = static_cast<uint32_t>(bits >> 32);
-                        w[15] = static_cast<uint32_t>(bits);
                         sha256_compress(sha, w);
                     }
                 }
+                if (kFeat && last && frm.n) emit_frame();
             }
 
             __syncwarp();          // every lane is done reading this stage
@@ -300,26 +327,28 @@ ingest_kernel(const IngestParams p)
                 r[0] = make_uint4(0, 0, 0, 0);
                 r[1] = make_uint4(0, 0, 0, 0);
             }
-            double sumsq = 0.0, rms = 0.0;
-            uint32_t nzc = 0, fl = flags << 8;
+            double rms = 0.0;
+            uint32_t fl = flags << 8;
             float pk = 0.0f;
             if (kFeat) {
-                sumsq = msg.sum; rms = msg.rms(); nzc = msg.nz; pk = msg.peak();
+                const uint32_t n = nb >> 1;
+                rms = n ? __dsqrt_rn(__ddiv_rn(msg_sum, static_cast<double>(n))) : 0.0;
+                pk = pcm_to_f32(msg_amax);
                 if (rms > p.vad) fl |= 1u;
             }
-            r[2] = make_uint4(__double2loint(sumsq), __double2hiint(sumsq), __double2loint(rms), __double2hiint(rms));
-            r[3] = make_uint4(nb >> 1, nzc, __float_as_uint(pk), fl);
+            r[2] = make_uint4(__double2loint(msg_sum), __double2hiint(msg_sum), __double2loint(rms), __double2hiint(rms));
+            r[3] = make_uint4(nb >> 1, msg_nz, __float_as_uint(pk), fl);
         }
     }
 }
 
 // ---------------------------------------------------------------- host launcher
-template <int CH, int STAGES, uint32_t MODE>
+template <int CH, int STAGES, uint32_t MODE, int MINB>
 static int launch_ingest(const IngestParams &p, cudaStream_t st)
 {
     using L = TileSmem<CH, STAGES>;
     constexpr int smem = kWarpsPerBlock * L::kWarpBytes;
-    auto kern = ingest_kernel<CH, STAGES, MODE>;
+    auto kern = ingest_kernel<CH, STAGES, MODE, MINB>;
     static thread_local int configured_dev = -1;
     static thread_local int blocks_per_sm = 0;
     int dev = 0;
@@ -370,14 +399,31 @@ extern "C" int ga_k_ingest(const void *d_pcm, const ga_desc *d_desc, uint32_t n_
     p.n_msgs = n_msgs;
     p.n_tiles = (n_msgs + 31) / 32;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    constexpr int CH = 128, ST = 3;
+    // Tuning variants for experiments (GA_INGEST_VARIANT=1..): the three bench modes only.
+    static const int variant = [] { const char *e = getenv("GA_INGEST_VARIANT"); return e ? atoi(e) : 0; }();
+    if (variant && (mode == 3 || mode == 4 || mode == 7)) {
+#define GA_V(ch, stg, minb)                                                 \
+        (mode == 3 ? launch_ingest<ch, stg, 3, minb>(p, st)                 \
+                   : mode == 4 ? launch_ingest<ch, stg, 4, minb>(p, st)     \
+                               : launch_ingest<ch, stg, 7, minb>(p, st))
+        switch (variant) {
+            case 1: return GA_V(128, 2, 5);
+            case 2: return GA_V(128, 2, 6);
+            case 3: return GA_V(256, 2, 3);
+            case 4: return GA_V(64, 4, 6);
+            case 5: return GA_V(128, 4, 3);
+            default: break;
+        }
+#undef GA_V
+    }
+    constexpr int CH = 128, ST = 3, MB = 1;
     switch (mode) {
-        case 1: return launch_ingest<CH, ST, 1>(p, st);
-        case 2: return launch_ingest<CH, ST, 2>(p, st);
-        case 3: return launch_ingest<CH, ST, 3>(p, st);
-        case 4: return launch_ingest<CH, ST, 4>(p, st);
-        case 5: return launch_ingest<CH, ST, 5>(p, st);
-        case 6: return launch_ingest<CH, ST, 6>(p, st);
-        default: return launch_ingest<CH, ST, 7>(p, st);
+        case 1: return launch_ingest<CH, ST, 1, MB>(p, st);
+        case 2: return launch_ingest<CH, ST, 2, MB>(p, st);
+        case 3: return launch_ingest<CH, ST, 3, MB>(p, st);
+        case 4: return launch_ingest<CH, ST, 4, MB>(p, st);
+        case 5: return launch_ingest<CH, ST, 5, MB>(p, st);
+        case 6: return launch_ingest<CH, ST, 6, MB>(p, st);
+        default: return launch_ingest<CH, ST, 7, MB>(p, st);
     }
 }

@@ -28,7 +28,7 @@ size_t ora_bytes_to_float32(const uint8_t *data, size_t len, float *out, ora_sta
         /* :1076 little-endian two's-complement int16 */
         int16_t val = (int16_t)((uint16_t)data[2 * i] | ((uint16_t)data[2 * i + 1] << 8));
         /* :1078 float32(val) / 32767.0 — an IEEE float32 division, RN-even */
-        volatile float q = (float)val / 32767.0f;
+        float q = (float)val / 32767.0f;   /* -ffp-contract=off, SSE: no excess precision */
         out[i] = q;
         if (q != 0.0f) nonzero++;                /* :1081-1083 */
         float a = q;                             /* :1084-1090 */
@@ -54,7 +54,7 @@ double ora_signal_strength(const float *samples, size_t n, ora_stats *st)
     float peak = 0.0f;
     for (size_t i = 0; i < n; i++) {             /* :827 */
         float s = samples[i];
-        volatile float sq = s * s;               /* :828 f32 product rounded to f32 ... */
+        float sq = s * s;                        /* :828 f32 product rounded to f32 ... */
         sum += (double)sq;                       /*      ... then widened, f64 add in index order */
         if (s != 0.0f) nonzero++;                /* :829-831 */
         float a = s;                             /* :832-838 */

@@ -222,6 +222,22 @@ def test_extreme_sample_values_and_silence(ctx):
     assert res["rms"][2] == 0.0 and res["nonzero"][2] == 0 and (res["flags"][2] & 1) == 0
 
 
+def test_peak_of_negative_samples_in_either_half(ctx):
+    """The peak must be found wherever the loudest sample sits and whatever its sign (this
+    caught an nvcc VIMNMX3 miscompile of the packed min/max statistics)."""
+    for val in (-32555, 32555, -32768):
+        for n in (320, 321, 37):
+            chunks = []
+            for pos in range(n):
+                v = np.full(n, 5, dtype="<i2"); v[pos] = val
+                chunks.append(v.tobytes())
+            res, _ = ctx.ingest(chunks, np.arange(n, dtype=np.uint32) % 256,
+                                np.full(n, L.MSG_FIRST, np.uint32))
+            want = np.abs(np.float32(val) / np.float32(32767.0))
+            assert (bits(res["peak"]) == bits(want)).all(), (val, n)
+            assert (res["nonzero"] == n).all()
+
+
 # ------------------------------------------------------------------ synthetic streams end to end
 def test_cfg1_single_stream_5s_utterance_as_250_chunks(ctx):
     """BASELINE.json configs[0]: one relay stream, 5 s of 16 kHz mono int16 in 20 ms chunks."""
