@@ -200,6 +200,11 @@ int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *ticket);
  * ticket's ring range.  Tickets must be waited in submission order. */
 int ga_wait(ga_ctx *ctx, uint64_t ticket, ga_result *results, ga_frame *frames);
 int ga_ticket_frames(ga_ctx *ctx, uint64_t ticket, uint32_t *n_frames);
+/* Same as ga_wait without the copy: returns pointers into the C-owned pinned result buffers of
+ * the ticket's slot (cgo wraps them with unsafe.Slice).  They stay valid until max_inflight
+ * further ga_submit calls have been made.  Any out pointer may be NULL. */
+int ga_wait_view(ga_ctx *ctx, uint64_t ticket, const ga_result **results, const ga_frame **frames,
+                 uint32_t *n_results, uint32_t *n_frames);
 
 /* Copy a stream's converted samples [first, first+n) to the host — what
  * RelayStream.WakeWordSignal ++ SpeechAudio holds (audio_service.go:592-594); used for

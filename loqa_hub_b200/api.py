@@ -152,6 +152,18 @@ class Context:
         check(load().ga_wait(self._h, ticket, ptr(res), ptr(frames)))
         return res, frames
 
+    def wait_view(self, ticket):
+        """Zero-copy wait: numpy views of the pinned result buffers (valid until max_inflight
+        further submits)."""
+        self._pending.pop(ticket)
+        pr, pf, nr, nf = C.c_void_p(), C.c_void_p(), C.c_uint32(), C.c_uint32()
+        check(load().ga_wait_view(self._h, ticket, C.byref(pr), C.byref(pf), C.byref(nr), C.byref(nf)))
+        res = np.ctypeslib.as_array(C.cast(pr, C.POINTER(C.c_uint8)), shape=(nr.value * 64,)).view(RESULT_DTYPE) \
+            if nr.value else np.zeros(0, RESULT_DTYPE)
+        frames = np.ctypeslib.as_array(C.cast(pf, C.POINTER(C.c_uint8)), shape=(nf.value * 32,)).view(FRAME_DTYPE) \
+            if nf.value else np.zeros(0, FRAME_DTYPE)
+        return res, frames
+
     def ingest(self, chunks, stream_ids, flags=None):
         """Convenience: push + submit + wait a list of byte chunks."""
         n = len(chunks)

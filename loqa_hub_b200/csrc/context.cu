@@ -252,80 +252,94 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
     const uint64_t head = ctx->ring_head.load(std::memory_order_acquire);
     const uint64_t tail = ctx->ring_tail.load(std::memory_order_acquire);
 
-    // pass 1: validate (no state is touched until the whole batch is known to be good)
-    for (uint32_t i = 0; i < n; i++) {
-        const ga_msg &m = msgs[i];
-        const uint64_t need = (static_cast<uint64_t>(m.nbytes) + 15u) & ~15ull;
-        if (m.stream_id >= ctx->cfg.max_streams) { set_error("ga_submit: msg %u: stream_id %u out of range", i, m.stream_id); return GA_ERR_ARG; }
-        if ((m.ring_offset & 15u) || m.ring_offset < tail || m.ring_offset + need > head || m.ring_offset % size + need > size) {
-            set_error("ga_submit: msg %u: ring_offset %llu not a live reservation", i, (unsigned long long)m.ring_offset);
-            return GA_ERR_ARG;
-        }
-    }
-    // pass 2: descriptors.  Stream cursors are advanced on a scratch copy first.
-    struct Touched { uint32_t id; StreamState before; };
-    std::vector<Touched> undo;
+    // One lean pass: validate, advance the stream cursors, write the descriptor, grow the H2D
+    // runs.  A bad message rolls the cursors of the messages before it back, so a failed
+    // submit leaves the context exactly as it was.
+    struct Saved { StreamState before; };
+    std::vector<Saved> resets;                 // only GA_MSG_FIRST messages need a saved state
     uint64_t release_to = tail, frames = 0;
     struct Run { uint64_t lo, hi; };
-    std::vector<Run> runs;
-    for (uint32_t i = 0; i < n; i++) {
+    Run runs[16];
+    int n_runs = 0;
+    bool scattered = false;
+    int err = GA_OK;
+    uint32_t i = 0;
+    ga_desc *descs = slot->h_desc;
+    StreamState *streams = ctx->streams.data();
+    const uint32_t max_streams = ctx->cfg.max_streams;
+    for (; i < n; i++) {
         const ga_msg &m = msgs[i];
-        StreamState &st = ctx->streams[m.stream_id];
-        undo.push_back({m.stream_id, st});
-        if (m.flags & GA_MSG_FIRST) st = StreamState();
-        const uint64_t ns = m.nbytes / 2;
-        ga_desc &d = slot->h_desc[i];
-        d.in_off = m.ring_offset % size;
+        const uint64_t need = (static_cast<uint64_t>(m.nbytes) + 15u) & ~15ull;
+        const uint64_t phys = m.ring_offset % size;
+        if (m.stream_id >= max_streams) { set_error("ga_submit: msg %u: stream_id %u out of range", i, m.stream_id); err = GA_ERR_ARG; break; }
+        if ((m.ring_offset & 15u) || m.ring_offset < tail || m.ring_offset + need > head || phys + need > size) {
+            set_error("ga_submit: msg %u: ring_offset %llu not a live reservation", i, (unsigned long long)m.ring_offset);
+            err = GA_ERR_ARG;
+            break;
+        }
+        StreamState &st = streams[m.stream_id];
+        if (m.flags & GA_MSG_FIRST) { resets.push_back({st}); st = StreamState(); }
+        const uint64_t ns = m.nbytes >> 1;
+        const bool is_wake = (m.flags & GA_MSG_WAKE) != 0;
+        uint64_t &cursor = is_wake ? st.wake_n : st.speech_n;   // audio_service.go:965 / :1002 append
+        ga_desc &d = descs[i];
+        d.in_off = phys;
         d.nbytes = m.nbytes;
         d.stream_id = m.stream_id;
         d.flags = m.flags;
         d.frame_off = static_cast<uint32_t>(frames);
         d.out_off = 0;
         if (convert) {
-            const uint64_t base = static_cast<uint64_t>(m.stream_id) * arena;
-            bool over;
-            if (m.flags & GA_MSG_WAKE) {           // audio_service.go:965 wakeWordBuffer = append(...)
-                over = st.wake_n + ns > wake_cap;
-                d.out_off = base + st.wake_n;
-                if (!over) st.wake_n += ns;
-            } else {                                // audio_service.go:1002 relay.SpeechAudio = append(...)
-                over = wake_cap + st.speech_n + ns > arena;
-                d.out_off = base + wake_cap + st.speech_n;
-                if (!over) st.speech_n += ns;
+            const uint64_t region = is_wake ? 0 : wake_cap, cap = is_wake ? wake_cap : arena - wake_cap;
+            if (cursor + ns > cap) {
+                if (m.flags & GA_MSG_FIRST) { st = resets.back().before; resets.pop_back(); }
+                set_error("ga_submit: msg %u overflows stream %u's %s sample arena", i, m.stream_id, is_wake ? "wake-word" : "speech");
+                err = GA_ERR_OVERFLOW;
+                break;
             }
-            if (over) {
-                for (auto it = undo.rbegin(); it != undo.rend(); ++it) ctx->streams[it->id] = it->before;
-                set_error("ga_submit: msg %u overflows stream %u's sample arena", i, m.stream_id);
-                return GA_ERR_OVERFLOW;
-            }
-        } else if (m.flags & GA_MSG_WAKE) {
-            st.wake_n += ns;
-        } else {
-            st.speech_n += ns;
+            d.out_off = static_cast<uint64_t>(m.stream_id) * arena + region + cursor;
         }
+        cursor += ns;
         frames += (ns + GA_FRAME_SAMPLES - 1) / GA_FRAME_SAMPLES;
-        const uint64_t need = (static_cast<uint64_t>(m.nbytes) + 15u) & ~15ull;
-        release_to = std::max(release_to, m.ring_offset + need);
+        const uint64_t end = m.ring_offset + need;
+        if (end > release_to) release_to = end;
         if (need) {
-            const uint64_t lo = d.in_off, hi = d.in_off + need;
-            if (!runs.empty() && lo >= runs.back().lo && lo <= runs.back().hi + 4096) runs.back().hi = std::max(runs.back().hi, hi);
-            else runs.push_back({lo, hi});
+            const uint64_t hi = phys + need;
+            if (n_runs && phys >= runs[n_runs - 1].lo && phys <= runs[n_runs - 1].hi + 4096) {
+                if (hi > runs[n_runs - 1].hi) runs[n_runs - 1].hi = hi;
+            } else if (n_runs < 16) {
+                runs[n_runs++] = {phys, hi};
+            } else {
+                scattered = true;
+                if (phys < runs[0].lo) runs[0].lo = phys;
+                if (hi > runs[0].hi) runs[0].hi = hi;
+            }
         }
     }
-    if (ctx->frames_cap && frames > ctx->frames_cap) {
-        for (auto it = undo.rbegin(); it != undo.rend(); ++it) ctx->streams[it->id] = it->before;
+    if (!err && ctx->frames_cap && frames > ctx->frames_cap) {
         set_error("ga_submit: batch needs %llu frame records, capacity %llu", (unsigned long long)frames, (unsigned long long)ctx->frames_cap);
-        return GA_ERR_OVERFLOW;
+        err = GA_ERR_OVERFLOW;
     }
-    if (runs.size() > 16) {   // scattered reservations: fall back to one covering copy
-        Run all = runs[0];
-        for (auto &r : runs) { all.lo = std::min(all.lo, r.lo); all.hi = std::max(all.hi, r.hi); }
-        runs.assign(1, all);
+    if (err) {                                  // undo messages i-1 .. 0
+        while (i-- > 0) {
+            const ga_msg &m = msgs[i];
+            StreamState &st = streams[m.stream_id];
+            ((m.flags & GA_MSG_WAKE) ? st.wake_n : st.speech_n) -= m.nbytes >> 1;
+            if (m.flags & GA_MSG_FIRST) { st = resets.back().before; resets.pop_back(); }
+        }
+        return err;
+    }
+    if (scattered) {   // more than 16 disjoint ranges: one covering copy
+        for (int r = 1; r < n_runs; r++) {
+            if (runs[r].lo < runs[0].lo) runs[0].lo = runs[r].lo;
+            if (runs[r].hi > runs[0].hi) runs[0].hi = runs[r].hi;
+        }
+        n_runs = 1;
     }
 
     cudaStream_t s = slot->stream;
-    for (auto &r : runs)
-        GA_CUDA_TRY(cudaMemcpyAsync(ctx->d_ring + r.lo, ctx->h_ring + r.lo, r.hi - r.lo, cudaMemcpyHostToDevice, s));
+    for (int r = 0; r < n_runs; r++)
+        GA_CUDA_TRY(cudaMemcpyAsync(ctx->d_ring + runs[r].lo, ctx->h_ring + runs[r].lo, runs[r].hi - runs[r].lo, cudaMemcpyHostToDevice, s));
     if (n) {
         GA_CUDA_TRY(cudaMemcpyAsync(slot->d_desc, slot->h_desc, sizeof(ga_desc) * n, cudaMemcpyHostToDevice, s));
         rc = ga_k_ingest(ctx->d_ring, slot->d_desc, n, ctx->d_arena, slot->d_res,
@@ -380,6 +394,35 @@ extern "C" int ga_wait(ga_ctx *ctx, uint64_t ticket, ga_result *results, ga_fram
     GA_CUDA_TRY(cudaEventSynchronize(s->done));     // outside the lock: submit may proceed meanwhile
     if (s->n_msgs) std::memcpy(results, s->h_res, sizeof(ga_result) * s->n_msgs);
     if (frames && ctx->frames_cap && s->n_frames) std::memcpy(frames, s->h_frames, sizeof(ga_frame) * s->n_frames);
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    uint64_t t = ctx->ring_tail.load(std::memory_order_relaxed);
+    if (s->release_to > t) ctx->ring_tail.store(s->release_to, std::memory_order_release);
+    s->busy = false;
+    ctx->oldest_ticket = ticket + 1;
+    return GA_OK;
+}
+
+extern "C" int ga_wait_view(ga_ctx *ctx, uint64_t ticket, const ga_result **results, const ga_frame **frames,
+                            uint32_t *n_results, uint32_t *n_frames)
+{
+    if (!ctx) { set_error("ga_wait_view: NULL context"); return GA_ERR_ARG; }
+    Slot *s;
+    {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        s = find_ticket(ctx, ticket);
+        if (!s) { set_error("ga_wait_view: unknown ticket %llu", (unsigned long long)ticket); return GA_ERR_STATE; }
+        if (ticket != ctx->oldest_ticket) {
+            set_error("ga_wait_view: tickets must be waited in submission order (oldest is %llu)", (unsigned long long)ctx->oldest_ticket);
+            return GA_ERR_STATE;
+        }
+    }
+    int rc = set_device(ctx);
+    if (rc) return rc;
+    GA_CUDA_TRY(cudaEventSynchronize(s->done));
+    if (results) *results = s->h_res;
+    if (frames) *frames = ctx->frames_cap ? s->h_frames : nullptr;
+    if (n_results) *n_results = s->n_msgs;
+    if (n_frames) *n_frames = ctx->frames_cap ? s->n_frames : 0;
     std::lock_guard<std::mutex> lk(ctx->mu);
     uint64_t t = ctx->ring_tail.load(std::memory_order_relaxed);
     if (s->release_to > t) ctx->ring_tail.store(s->release_to, std::memory_order_release);

@@ -6,20 +6,25 @@
 //   calculateSignalStrength      internal/grpc/audio_service.go:818-852     (sumsq / rms / nonzero / peak)
 //   voice-event audio fingerprint (README.md:50, API.md:170; hook events/voice_event.go:84-88)
 //
-// Work decomposition.  A warp owns a tile of 32 consecutive messages and streams them
-// through shared memory in CH-byte slices per message ("rows"): every lane issues one
-// TMA bulk copy (cp.async.bulk -> UBLKCP) for its own row into a STAGES-deep ring of
-// stage buffers, completion is tracked by one mbarrier per stage.  Each slice is then
-// consumed twice from shared memory:
-//   phase A (warp-cooperative, coalesced): 4 samples per lane -> one 16-byte streaming
-//           store of f32 samples; two rows per warp instruction, 256 B contiguous each;
-//   phase B (lane = message): the lane walks ITS message's 64-byte blocks: the SHA-256
-//           compression (schedule in registers) and the reference's strictly sequential
-//           float64 sum of float32 squares, so sumsq/rms are bit-identical to the Go loop.
-// Rows are padded by 16 B so the lane-per-row LDS.128 pattern is bank-conflict free.
-// The integer ALU pipe (SHA-256, ~22 instructions per byte) bounds the fused kernel; the
-// convert/feature-only instantiation is HBM-bound.  No tensor cores: nothing here is a
-// contraction.
+// Work decomposition.  A warp owns a tile of 32 consecutive messages; lane = message.
+// Messages are streamed through shared memory in CH-byte slices ("rows"): every lane issues
+// one TMA bulk copy (cp.async.bulk -> UBLKCP) for its own row into a STAGES-deep ring of
+// stage buffers, completion is tracked by one mbarrier per stage.  The lane then walks ITS
+// row's 64-byte blocks: each int16 pair is converted (exact division), fed to the reference's
+// strictly sequential float64 sum of float32 squares (so sumsq/rms are bit-identical to the
+// Go loop) and to the packed statistics, and the block is hashed (SHA-256 schedule in
+// registers).  Rows are padded by 16 B so the lane-per-row LDS.128 pattern is bank-conflict
+// free.  The f32 samples leave the SM in one of two ways (template parameter COOP):
+//   COOP = 0  the lane stores its own samples, 16 bytes per instruction.  Uncoalesced across
+//             lanes (L2 merges the sectors), but it needs no second pass, no shuffles and only
+//             one division per sample — best when the kernel is bound by the integer ALU pipe,
+//             i.e. whenever SHA-256 runs (measured 1.20 ms vs 1.36 ms per 20,480 audio-s).
+//   COOP = 1  a warp-cooperative pass converts the slice again with 4 samples per lane and
+//             writes 256 contiguous bytes per row — best for the HBM-bound instantiations
+//             without SHA-256 (0.43 ms vs 0.91 ms).
+// A third variant staged the samples in shared memory and used TMA bulk stores; with 128-256 B
+// per store and the proxy fence it was slower than both (tuning log).
+// No tensor cores: nothing here is a contraction.
 #include <cstdlib>
 
 #include "common.cuh"
@@ -33,7 +38,8 @@ template <int CH, int STAGES>
 struct TileSmem {
     static constexpr int kRowStride = CH + 16;          // (CH/16 + 1) is odd -> conflict-free LDS.128
     static constexpr int kStageBytes = 32 * kRowStride;
-    static constexpr int kWarpBytes = STAGES * kStageBytes + 128;   // + barriers (padded)
+    static constexpr int kBarBase = STAGES * kStageBytes;
+    static constexpr int kWarpBytes = kBarBase + 128;   // + barriers (padded)
     static_assert(CH % 64 == 0, "slices must hold whole SHA-256 blocks");
     static_assert(((CH / 16) + 1) % 2 == 1, "row stride must be an odd number of 16-byte units");
 };
@@ -87,11 +93,13 @@ struct Span {
     }
 };
 
-template <int CH, int STAGES, uint32_t MODE, int MINB>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32, MINB)
+template <int CH, int STAGES, uint32_t MODE, int COOP>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
 ingest_kernel(const IngestParams p)
 {
     using L = TileSmem<CH, STAGES>;
+    constexpr bool kCoop = (MODE & GA_DO_CONVERT) != 0 && COOP == 1;      // cooperative store pass
+    constexpr bool kLaneStore = (MODE & GA_DO_CONVERT) != 0 && COOP == 0; // lane stores its own samples
     constexpr bool kConvert = (MODE & GA_DO_CONVERT) != 0;
     constexpr bool kFeat = (MODE & GA_DO_FEATURES) != 0;
     constexpr bool kSha = (MODE & GA_DO_SHA256) != 0;
@@ -100,7 +108,7 @@ ingest_kernel(const IngestParams p)
     extern __shared__ __align__(128) uint8_t smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint8_t *wbase = smem + warp * L::kWarpBytes;
-    uint64_t *bars = reinterpret_cast<uint64_t *>(wbase + STAGES * L::kStageBytes);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(wbase + L::kBarBase);
 
     if (lane == 0) {
 #pragma unroll
@@ -191,9 +199,9 @@ ingest_kernel(const IngestParams p)
             fidx++;
             frm.reset();
         };
-        // one sample, already exact as a float, in reference order (audio_service.go:827-828)
-        auto chain = [&](float v) {
-            const double q = sq_f64(pcm_to_f32(v));
+        // one converted sample in reference order (audio_service.go:827-828)
+        auto chain = [&](float x) {
+            const double q = sq_f64(x);
             msg_sum += q;
             frm.sum += q;
         };
@@ -205,8 +213,8 @@ ingest_kernel(const IngestParams p)
             const uint32_t lo = c * CH;
             mbar_wait(&bars[stage], parity);
 
-            // ---------------- phase A: cooperative convert + coalesced store
-            if (kConvert) {
+            // ---------------- cooperative convert + coalesced store (COOP = 1)
+            if (kCoop) {
                 constexpr int VPR = CH / 8;   // 4-sample vectors per row slice
 #pragma unroll 4
                 for (int k = 0; k < VPR; k++) {
@@ -236,10 +244,10 @@ ingest_kernel(const IngestParams p)
                 }
             }
 
-            // ---------------- phase B: lane = message.  One loop over the 64-byte blocks this
-            // slice contributes, including the padding block(s) when the message ends here, so
-            // the unrolled compression exists once in the instruction stream.
-            if ((kFeat || kSha) && c < my_nch) {
+            // ---------------- lane = message.  One loop over the 64-byte blocks this slice
+            // contributes, including the padding block(s) when the message ends here, so the
+            // unrolled compression exists once in the instruction stream.
+            if ((kFeat || kSha || kLaneStore) && c < my_nch) {
                 const uint8_t *rowp = sbase + lane * L::kRowStride;
                 const uint32_t span = min(nb, lo + CH) - lo;
                 const uint32_t nfull = span >> 6;
@@ -260,30 +268,47 @@ ingest_kernel(const IngestParams p)
 #pragma unroll
                         for (int j = 0; j < 16; j++) w[j] = 0;
                     }
-                    if (kFeat) {
+                    if (kFeat || kLaneStore) {
                         if (vb == 64) {
+                            float *g = p.samples + out_off + (lo >> 1) + b * 32;
+                            const bool galigned = (out_off & 3ull) == 0;
 #pragma unroll
-                            for (int j = 0; j < 16; j++) {
-                                float a, bb;
-                                unpack2(w[j], a, bb);
-                                chain(a);
-                                chain(bb);
-                                frm.stats_word(w[j]);
+                            for (int j = 0; j < 16; j += 2) {
+                                float v0, v1, v2, v3;
+                                unpack2(w[j], v0, v1);
+                                unpack2(w[j + 1], v2, v3);
+                                const float x0 = pcm_to_f32(v0), x1 = pcm_to_f32(v1);
+                                const float x2 = pcm_to_f32(v2), x3 = pcm_to_f32(v3);
+                                if (kLaneStore) {
+                                    if (galigned) st_global_v4(g + 2 * j, x0, x1, x2, x3);
+                                    else { g[2 * j] = x0; g[2 * j + 1] = x1; g[2 * j + 2] = x2; g[2 * j + 3] = x3; }
+                                }
+                                if (kFeat) {
+                                    chain(x0); chain(x1); chain(x2); chain(x3);
+                                    frm.stats_word(w[j]);
+                                    frm.stats_word(w[j + 1]);
+                                }
                             }
-                            frm.n += 32;
-                            if (frm.n == GA_FRAME_SAMPLES) emit_frame();
+                            if (kFeat) {
+                                frm.n += 32;
+                                if (frm.n == GA_FRAME_SAMPLES) emit_frame();
+                            }
                         } else if (vb >= 2) {
                             // tail of the message: fewer than 32 samples, rolled loop from shared memory
                             const uint32_t ns = vb >> 1;           // an odd trailing byte is not a sample
                             const uint16_t *hp = reinterpret_cast<const uint16_t *>(rowp + b * 64);
                             for (uint32_t k = 0; k < ns; k++) {
                                 const uint32_t h = hp[k];
-                                float a, bb;
-                                unpack2(h, a, bb);
-                                chain(a);
-                                frm.stats_word(h);                  // upper half is a zero sample: neutral
+                                float v0, v1;
+                                unpack2(h, v0, v1);
+                                const float x0 = pcm_to_f32(v0);
+                                if (kLaneStore) p.samples[out_off + (lo >> 1) + b * 32 + k] = x0;
+                                if (kFeat) {
+                                    chain(x0);
+                                    frm.stats_word(h);              // upper half is a zero sample: neutral
+                                }
                             }
-                            frm.n += ns;
+                            if (kFeat) frm.n += ns;
                         }
                     }
                     if (kSha) {
@@ -311,6 +336,7 @@ ingest_kernel(const IngestParams p)
                     }
                 }
                 if (kFeat && last && frm.n) emit_frame();
+
             }
 
             __syncwarp();          // every lane is done reading this stage
@@ -343,12 +369,12 @@ ingest_kernel(const IngestParams p)
 }
 
 // ---------------------------------------------------------------- host launcher
-template <int CH, int STAGES, uint32_t MODE, int MINB>
+template <int CH, int STAGES, uint32_t MODE, int COOP>
 static int launch_ingest(const IngestParams &p, cudaStream_t st)
 {
     using L = TileSmem<CH, STAGES>;
     constexpr int smem = kWarpsPerBlock * L::kWarpBytes;
-    auto kern = ingest_kernel<CH, STAGES, MODE, MINB>;
+    auto kern = ingest_kernel<CH, STAGES, MODE, COOP>;
     static thread_local int configured_dev = -1;
     static thread_local int blocks_per_sm = 0;
     int dev = 0;
@@ -402,28 +428,30 @@ extern "C" int ga_k_ingest(const void *d_pcm, const ga_desc *d_desc, uint32_t n_
     // Tuning variants for experiments (GA_INGEST_VARIANT=1..): the three bench modes only.
     static const int variant = [] { const char *e = getenv("GA_INGEST_VARIANT"); return e ? atoi(e) : 0; }();
     if (variant && (mode == 3 || mode == 4 || mode == 7)) {
-#define GA_V(ch, stg, minb)                                                 \
-        (mode == 3 ? launch_ingest<ch, stg, 3, minb>(p, st)                 \
-                   : mode == 4 ? launch_ingest<ch, stg, 4, minb>(p, st)     \
-                               : launch_ingest<ch, stg, 7, minb>(p, st))
+#define GA_V(ch, stg, coop)                                                 \
+        (mode == 3 ? launch_ingest<ch, stg, 3, coop>(p, st)                 \
+                   : mode == 4 ? launch_ingest<ch, stg, 4, coop>(p, st)     \
+                               : launch_ingest<ch, stg, 7, coop>(p, st))
         switch (variant) {
-            case 1: return GA_V(128, 2, 5);
-            case 2: return GA_V(128, 2, 6);
-            case 3: return GA_V(256, 2, 3);
-            case 4: return GA_V(64, 4, 6);
-            case 5: return GA_V(128, 4, 3);
+            case 1: return GA_V(128, 3, 0);
+            case 2: return GA_V(128, 3, 1);
+            case 3: return GA_V(128, 2, 1);
+            case 4: return GA_V(256, 2, 0);
+            case 5: return GA_V(256, 2, 1);
+            case 6: return GA_V(128, 4, 1);
             default: break;
         }
 #undef GA_V
     }
-    constexpr int CH = 128, ST = 3, MB = 1;
+    // Defaults from the tuning sweep: lane stores when SHA-256 runs (ALU-bound),
+    // the cooperative coalesced store pass otherwise (HBM-bound).
     switch (mode) {
-        case 1: return launch_ingest<CH, ST, 1, MB>(p, st);
-        case 2: return launch_ingest<CH, ST, 2, MB>(p, st);
-        case 3: return launch_ingest<CH, ST, 3, MB>(p, st);
-        case 4: return launch_ingest<CH, ST, 4, MB>(p, st);
-        case 5: return launch_ingest<CH, ST, 5, MB>(p, st);
-        case 6: return launch_ingest<CH, ST, 6, MB>(p, st);
-        default: return launch_ingest<CH, ST, 7, MB>(p, st);
+        case 1: return launch_ingest<128, 2, 1, 1>(p, st);
+        case 2: return launch_ingest<128, 2, 2, 1>(p, st);
+        case 3: return launch_ingest<128, 2, 3, 1>(p, st);
+        case 4: return launch_ingest<128, 3, 4, 0>(p, st);
+        case 5: return launch_ingest<128, 2, 5, 0>(p, st);
+        case 6: return launch_ingest<128, 2, 6, 0>(p, st);
+        default: return launch_ingest<128, 2, 7, 0>(p, st);
     }
 }
