@@ -142,6 +142,29 @@ int ga_k_signal_strength(const float *d_samples, const uint64_t *d_wake_off, con
 int ga_k_select(const double *d_scores, const uint8_t *d_status_in, const uint32_t *d_seg_offsets,
                 uint32_t n_windows, uint32_t *d_winner, uint8_t *d_status_out, void *stream);
 
+/* ga_k_arbitrate for callers that cannot allocate GPU memory.  (No counterpart in the
+ * reference: the Go hub has no device memory at all.  It exists for hosts of this library whose
+ * arbitration call sits where cudaMalloc is off limits — a hub process that hands its whole HBM
+ * budget to its own pool at start-up, or a window-close timer path that must not take the
+ * device-wide synchronisation an allocation implies while other streams are ingesting.)
+ *
+ * Inputs, rules and outputs are those of ga_k_arbitrate, minus the score array: the caller gets
+ * winner[] and status_out[] only.  The per-member float64 scores, which sit between the scoring
+ * launch and the selection launch, live in a 512 KiB array built into the library image; every
+ * GPU the library is loaded on holds one copy until the process exits.  Consequences:
+ *   - n_members may be at most 65,536 per call; more is refused with GA_ERR_OVERFLOW (split the
+ *     windows over several calls, or use ga_k_arbitrate with a score array of your own);
+ *   - the call makes no cudaMalloc / cudaFree and uses no allocating library routine;
+ *   - all calls on one GPU share the array and it keeps the last call's scores; each call first
+ *     zeroes the slots it is going to use.  Two calls that overlap on the GPU (different streams,
+ *     or different threads without ordering) race on it — serialise them on one stream or with
+ *     events;
+ *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress,
+ *     with that device current); make that first call before any stream capture begins. */
+int ga_k_arbitrate_noalloc(const float *d_samples, const uint64_t *d_wake_off, const uint32_t *d_wake_n,
+                           const uint8_t *d_status_in, const uint32_t *d_seg_offsets, uint32_t n_windows,
+                           uint32_t n_members, uint32_t *d_winner, uint8_t *d_status_out, void *stream);
+
 /* Cross-shard windows: scatter scores that arrived from other shards
  * (d_gathered, the all-gathered guest scores) into this shard's member slots:
  * d_scores[dst_slot[i]] = d_gathered[src_idx[i]].  Runs between the scoring launch and

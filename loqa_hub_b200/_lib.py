@@ -45,6 +45,7 @@ _vp, _u32, _u64, _i32, _sz = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int, C.c_si
 SYMBOLS = {
     "ga_k_ingest": (_i32, [_vp, _vp, _u32, _vp, _vp, _vp, _u32, C.c_double, _vp]),
     "ga_k_arbitrate": (_i32, [_vp, _vp, _vp, _vp, _vp, _u32, _u32, _vp, _vp, _vp, _vp]),
+    "ga_k_arbitrate_noalloc": (_i32, [_vp, _vp, _vp, _vp, _vp, _u32, _u32, _vp, _vp, _vp]),
     "ga_k_signal_strength": (_i32, [_vp, _vp, _vp, _vp, _u32, _vp, _vp, _vp]),
     "ga_k_select": (_i32, [_vp, _vp, _vp, _u32, _vp, _vp, _vp]),
     "ga_k_route_scores": (_i32, [_vp, _vp, _vp, _u32, _vp, _vp]),

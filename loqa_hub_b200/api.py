@@ -44,6 +44,12 @@ def k_arbitrate(d_samples, d_wake_off, d_wake_n, d_status_in, d_seg, n_windows, 
                                 n_members, d_scores, d_winner, d_status_out, stream or None))
 
 
+def k_arbitrate_noalloc(d_samples, d_wake_off, d_wake_n, d_status_in, d_seg, n_windows, n_members,
+                        d_winner, d_status_out, stream=0):
+    check(load().ga_k_arbitrate_noalloc(d_samples, d_wake_off, d_wake_n, d_status_in, d_seg, n_windows,
+                                        n_members, d_winner, d_status_out, stream or None))
+
+
 def k_signal_strength(d_samples, d_wake_off, d_wake_n, d_status_in, n_members, d_scores,
                       d_stats=0, stream=0):
     check(load().ga_k_signal_strength(d_samples, d_wake_off, d_wake_n, d_status_in or None,

@@ -13,6 +13,8 @@
 //                  member when nothing exceeded 0.0 (:542-547) — then Winner / Cancelled
 //                  for every member (:553-571).  Join order stands in for Go's random map
 //                  iteration order.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace ga {
@@ -229,4 +231,68 @@ extern "C" int ga_k_arbitrate(const float *d_samples, const uint64_t *d_wake_off
     int rc = launch_scores(d_samples, d_wake_off, d_wake_n, d_status_in, n_members, d_scores, nullptr, st);
     if (rc) return rc;
     return launch_select(d_scores, d_status_in, d_seg_offsets, n_windows, d_winner, d_status_out, st);
+}
+
+// ---------------------------------------------------------------- arbitration without allocation
+// Scratch for ga_k_arbitrate_noalloc: the per-member float64 scores that sit between the
+// scoring launch and the selection launch.  One copy lives in every GPU's memory from the
+// moment the library is loaded on it until the process exits (512 KiB).
+#define GA_NOALLOC_MAX_MEMBERS 65536u
+static __device__ __align__(256) double g_noalloc_scores[GA_NOALLOC_MAX_MEMBERS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+double *g_noalloc_ptr[kMaxDevices];     // device address of g_noalloc_scores, per device ordinal
+bool g_noalloc_ready[kMaxDevices];
+std::mutex g_noalloc_mu;
+}  // namespace
+
+// Winners and statuses of many collision windows for callers that must not allocate.
+// Same inputs, rules and outputs as ga_k_arbitrate, except that the scores are not returned:
+// they are kept in g_noalloc_scores.  See include/gpuaudio.h for the contract.
+extern "C" int ga_k_arbitrate_noalloc(const float *d_samples, const uint64_t *d_wake_off,
+                                      const uint32_t *d_wake_n, const uint8_t *d_status_in,
+                                      const uint32_t *d_seg_offsets, uint32_t n_windows, uint32_t n_members,
+                                      uint32_t *d_winner, uint8_t *d_status_out, void *stream)
+{
+    using namespace ga;
+    if (n_windows == 0) return GA_OK;
+    if (!d_seg_offsets || !d_winner) { set_error("ga_k_arbitrate_noalloc: NULL argument"); return GA_ERR_ARG; }
+    if (n_members && (!d_samples || !d_wake_off || !d_wake_n || !d_status_in || !d_status_out)) {
+        set_error("ga_k_arbitrate_noalloc: NULL argument");
+        return GA_ERR_ARG;
+    }
+    if (n_members > GA_NOALLOC_MAX_MEMBERS) {
+        set_error("ga_k_arbitrate_noalloc: %u window members exceed the built-in scratch of %u; "
+                  "split the windows over several calls or use ga_k_arbitrate with your own score array",
+                  n_members, GA_NOALLOC_MAX_MEMBERS);
+        return GA_ERR_OVERFLOW;
+    }
+    if (reinterpret_cast<uintptr_t>(d_samples) & 15u) {
+        set_error("ga_k_arbitrate_noalloc: d_samples must be 16-byte aligned");
+        return GA_ERR_ARG;
+    }
+    int dev = 0;
+    GA_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) { set_error("ga_k_arbitrate_noalloc: device ordinal %d not supported", dev); return GA_ERR_ARG; }
+    double *scores = nullptr;
+    {
+        // Set-up, once per device, with that device current: the name g_noalloc_scores is only a
+        // host-side handle, a kernel needs the address the symbol has on THIS device.
+        std::lock_guard<std::mutex> lk(g_noalloc_mu);
+        if (!g_noalloc_ready[dev]) {
+            double *p = nullptr;
+            GA_CUDA_TRY(cudaGetSymbolAddress(reinterpret_cast<void **>(&p), g_noalloc_scores));
+            g_noalloc_ptr[dev] = p;
+            g_noalloc_ready[dev] = true;
+        }
+        scores = g_noalloc_ptr[dev];
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    // The array still holds the previous call's scores: start this call's slots at 0.0 so a member
+    // the scorer skips (not contending) reads as "no signal", never as someone else's old score.
+    if (n_members) GA_CUDA_TRY(cudaMemsetAsync(scores, 0, sizeof(double) * n_members, st));
+    int rc = launch_scores(d_samples, d_wake_off, d_wake_n, d_status_in, n_members, scores, nullptr, st);
+    if (rc) return rc;
+    return launch_select(scores, d_status_in, d_seg_offsets, n_windows, d_winner, d_status_out, st);
 }
