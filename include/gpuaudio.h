@@ -142,6 +142,37 @@ int ga_k_signal_strength(const float *d_samples, const uint64_t *d_wake_off, con
 int ga_k_select(const double *d_scores, const uint8_t *d_status_in, const uint32_t *d_seg_offsets,
                 uint32_t n_windows, uint32_t *d_winner, uint8_t *d_status_out, void *stream);
 
+/* Descriptor of one 48 kHz interleaved-stereo int16 message for ga_k_resample48, 64 bytes. */
+#define GA_HIST_ZERO   0u   /* stream start: the 47 frames before the message are silence          */
+#define GA_HIST_SLAB   1u   /* they are in the PCM slab at hist_off (tail of the previous message)  */
+#define GA_HIST_STATE  2u   /* they are in d_hist_state[stream_id] (saved by an earlier launch)     */
+#define GA_RS_SAVE_HIST 0x10000u  /* flags bit: save this message's last 47 frames to d_hist_state  */
+#define GA_RS_MAX_MSG_BYTES 3840u /* one launch handles messages of up to 960 frames (20 ms)        */
+typedef struct ga_rdesc {
+    uint64_t in_off;     /* byte offset of the message in the PCM slab; multiple of 16            */
+    uint64_t out_off;    /* index of its first OUTPUT sample in the f32 arena                     */
+    uint64_t hist_off;   /* GA_HIST_SLAB: byte offset of the 47 preceding frames (multiple of 4)  */
+    uint64_t n0;         /* absolute index (since stream start) of the message's first frame      */
+    uint32_t nbytes;     /* <= GA_RS_MAX_MSG_BYTES; a trailing partial frame is dropped           */
+    uint32_t stream_id;
+    uint32_t flags;      /* GA_MSG_* | GA_RS_SAVE_HIST                                            */
+    uint32_t frame_off;
+    uint32_t hist_kind;  /* GA_HIST_*                                                             */
+    uint32_t reserved[3];
+} ga_rdesc;
+
+/* 48 kHz stereo -> 16 kHz mono ÷3 decimator + statistics of the resampled samples (BASELINE
+ * configs[3]).  New spec, no reference counterpart: the reference ignores AudioChunk.SampleRate
+ * (audio_service.go:926-1043).  Per message: mono = (A1(L) + A1(R)) * 0.5f with A1 the
+ * reference's conversion (:1078); y[M] = sum over the committed 48 taps (include/gpuaudio_taps.h)
+ * in fixed order with fused multiply-adds, on the stream's absolute frame timeline; then
+ * results[i].{sumsq,rms,n_samples,nonzero,peak,flags} (and frames) over y as in ga_k_ingest.
+ * The digest field of results[i] is not written (run ga_k_ingest with GA_DO_SHA256 on the same
+ * slab for the fingerprint of the received bytes).  d_hist_state: 192 bytes per stream. */
+int ga_k_resample48(const void *d_pcm, const ga_rdesc *d_desc, uint32_t n_msgs, void *d_hist_state,
+                    float *d_samples, ga_result *d_results, ga_frame *d_frames,
+                    double vad_threshold, void *stream);
+
 /* ga_k_arbitrate for callers that cannot allocate GPU memory.  (No counterpart in the
  * reference: the Go hub has no device memory at all.  It exists for hosts of this library whose
  * arbitration call sits where cudaMalloc is off limits — a hub process that hands its whole HBM
@@ -190,7 +221,14 @@ typedef struct ga_config {
     uint32_t mode;              /* GA_DO_* bits                                        */
     uint32_t want_frames;       /* != 0: per-frame records are produced and returned   */
     double   vad_threshold;     /* VAD flag = rms > threshold (default 0.01)           */
+    uint32_t input_format;      /* GA_FMT_*: what every message of this context holds  */
+    uint32_t reserved;
 } ga_config;
+#define GA_FMT_MONO16K   0u     /* 16 kHz mono int16 — what the reference assumes (:609) */
+#define GA_FMT_STEREO48K 1u     /* 48 kHz interleaved stereo int16, resampled to 16 kHz mono;
+                                   chunks of at most GA_RS_MAX_MSG_BYTES; a chunk that follows
+                                   another chunk of its stream in the SAME ga_submit needs that
+                                   predecessor to hold at least 47 frames                    */
 
 /* audio_service.go:233-244 is where the hub would call this (createAudioService). */
 int  ga_init(const ga_config *cfg, ga_ctx **out);
@@ -279,6 +317,11 @@ int ga_synth_fill_batch_device(void *d_pcm, uint64_t seed, uint32_t group_base,
 int ga_synth_fill_batch_device_map(void *d_pcm, uint64_t seed, const uint32_t *d_group,
                                    const uint32_t *d_relay, uint32_t n_streams, uint32_t n_msgs,
                                    uint32_t msg_samples, void *stream);
+/* 48 kHz interleaved-stereo version (configs[3]): 3x zero-order hold of the 16 kHz relay view,
+ * R = L - (L >> 3); message m of stream s at d_pcm + (m*n_streams + s)*msg_frames*4. */
+int ga_synth_fill_batch48_device_map(void *d_pcm, uint64_t seed, const uint32_t *d_group,
+                                     const uint32_t *d_relay, uint32_t n_streams, uint32_t n_msgs,
+                                     uint32_t msg_frames, void *stream);
 /* Same batch layout, filled on the host with n_threads workers (CPU-baseline input). */
 int ga_synth_fill_batch_host(void *pcm, uint64_t seed, uint32_t group_base, uint32_t n_streams,
                              uint32_t group_size, uint32_t n_msgs, uint32_t msg_samples,
@@ -287,8 +330,8 @@ int ga_synth_fill_batch_host(void *pcm, uint64_t seed, uint32_t group_base, uint
 /* Introspection for harnesses. */
 uint64_t ga_launch_count(void);            /* kernels launched by this library so far */
 int      ga_abi_version(void);
-/* sizes of {ga_result, ga_frame, ga_desc, ga_msg, ga_config} for binding self-checks */
-void     ga_abi_sizes(uint32_t out[5]);
+/* sizes of {ga_result, ga_frame, ga_desc, ga_msg, ga_config, ga_rdesc} for binding self-checks */
+void     ga_abi_sizes(uint32_t out[6]);
 int      ga_device_count(void);
 
 #ifdef __cplusplus

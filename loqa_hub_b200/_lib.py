@@ -30,20 +30,27 @@ DESC_DTYPE = np.dtype([("in_off", "<u8"), ("out_off", "<u8"), ("nbytes", "<u4"),
 MSG_DTYPE = np.dtype([("ring_offset", "<u8"), ("nbytes", "<u4"), ("stream_id", "<u4"),
                       ("flags", "<u4"), ("reserved", "<u4")])
 assert RESULT_DTYPE.itemsize == 64 and FRAME_DTYPE.itemsize == 32
-assert DESC_DTYPE.itemsize == 32 and MSG_DTYPE.itemsize == 24
+RDESC_DTYPE = np.dtype([("in_off", "<u8"), ("out_off", "<u8"), ("hist_off", "<u8"), ("n0", "<u8"),
+                        ("nbytes", "<u4"), ("stream_id", "<u4"), ("flags", "<u4"), ("frame_off", "<u4"),
+                        ("hist_kind", "<u4"), ("reserved", "<u4", 3)])
+HIST_ZERO, HIST_SLAB, HIST_STATE = 0, 1, 2
+RS_SAVE_HIST = 0x10000
+FMT_MONO16K, FMT_STEREO48K = 0, 1
+assert DESC_DTYPE.itemsize == 32 and MSG_DTYPE.itemsize == 24 and RDESC_DTYPE.itemsize == 64
 
 
 class Config(C.Structure):
     _fields_ = [("device", C.c_int32), ("max_streams", C.c_uint32), ("max_batch_msgs", C.c_uint32),
                 ("max_inflight", C.c_uint32), ("ring_bytes", C.c_uint64), ("arena_samples", C.c_uint64),
                 ("wake_samples_max", C.c_uint64), ("mode", C.c_uint32), ("want_frames", C.c_uint32),
-                ("vad_threshold", C.c_double)]
+                ("vad_threshold", C.c_double), ("input_format", C.c_uint32), ("reserved", C.c_uint32)]
 
 
 # every symbol include/gpuaudio.h declares: name -> (restype, argtypes)
 _vp, _u32, _u64, _i32, _sz = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int, C.c_size_t
 SYMBOLS = {
     "ga_k_ingest": (_i32, [_vp, _vp, _u32, _vp, _vp, _vp, _u32, C.c_double, _vp]),
+    "ga_k_resample48": (_i32, [_vp, _vp, _u32, _vp, _vp, _vp, _vp, C.c_double, _vp]),
     "ga_k_arbitrate": (_i32, [_vp, _vp, _vp, _vp, _vp, _u32, _u32, _vp, _vp, _vp, _vp]),
     "ga_k_arbitrate_noalloc": (_i32, [_vp, _vp, _vp, _vp, _vp, _u32, _u32, _vp, _vp, _vp]),
     "ga_k_signal_strength": (_i32, [_vp, _vp, _vp, _vp, _u32, _vp, _vp, _vp]),
@@ -68,10 +75,11 @@ SYMBOLS = {
     "ga_synth_fill_host": (_i32, [_vp, _u64, _u32, _u32, _u32, _u32, _u32]),
     "ga_synth_fill_batch_device": (_i32, [_vp, _u64, _u32, _u32, _u32, _u32, _u32, _vp]),
     "ga_synth_fill_batch_device_map": (_i32, [_vp, _u64, _vp, _vp, _u32, _u32, _u32, _vp]),
+    "ga_synth_fill_batch48_device_map": (_i32, [_vp, _u64, _vp, _vp, _u32, _u32, _u32, _vp]),
     "ga_synth_fill_batch_host": (_i32, [_vp, _u64, _u32, _u32, _u32, _u32, _u32, _u32]),
     "ga_launch_count": (_u64, []),
     "ga_abi_version": (_i32, []),
-    "ga_abi_sizes": (None, [C.POINTER(_u32 * 5)]),
+    "ga_abi_sizes": (None, [C.POINTER(_u32 * 6)]),
     "ga_device_count": (_i32, []),
 }
 
@@ -98,10 +106,10 @@ def load():
         fn = getattr(lib, name)      # AttributeError if the .so does not export it
         fn.restype = res
         fn.argtypes = args
-    sizes = (_u32 * 5)()
+    sizes = (_u32 * 6)()
     lib.ga_abi_sizes(C.byref(sizes))
     want = [RESULT_DTYPE.itemsize, FRAME_DTYPE.itemsize, DESC_DTYPE.itemsize, MSG_DTYPE.itemsize,
-            C.sizeof(Config)]
+            C.sizeof(Config), RDESC_DTYPE.itemsize]
     if list(sizes) != want:
         raise ImportError("libgpuaudio ABI struct sizes %s != binding %s" % (list(sizes), want))
     _lib = lib

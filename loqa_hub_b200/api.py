@@ -38,6 +38,12 @@ def k_ingest(d_pcm, d_desc, n_msgs, d_samples, d_results, d_frames=0, mode=L.DO_
                              mode, vad_threshold, stream or None))
 
 
+def k_resample48(d_pcm, d_rdesc, n_msgs, d_hist_state, d_samples, d_results, d_frames=0,
+                 vad_threshold=0.01, stream=0):
+    check(load().ga_k_resample48(d_pcm, d_rdesc, n_msgs, d_hist_state or None, d_samples, d_results,
+                                 d_frames or None, vad_threshold, stream or None))
+
+
 def k_arbitrate(d_samples, d_wake_off, d_wake_n, d_status_in, d_seg, n_windows, n_members,
                 d_scores, d_winner, d_status_out, stream=0):
     check(load().ga_k_arbitrate(d_samples, d_wake_off, d_wake_n, d_status_in, d_seg, n_windows,
@@ -68,6 +74,11 @@ def k_route_scores(d_gathered, d_src_idx, d_dst_slot, n, d_scores, stream=0):
 def synth_batch_device_map(d_pcm, seed, d_group, d_relay, n_streams, n_msgs, msg_samples, stream=0):
     check(load().ga_synth_fill_batch_device_map(d_pcm, seed, d_group, d_relay, n_streams, n_msgs,
                                                 msg_samples, stream or None))
+
+
+def synth_batch48_device_map(d_pcm, seed, d_group, d_relay, n_streams, n_msgs, msg_frames, stream=0):
+    check(load().ga_synth_fill_batch48_device_map(d_pcm, seed, d_group, d_relay, n_streams, n_msgs,
+                                                  msg_frames, stream or None))
 
 
 def launch_count():
@@ -105,10 +116,10 @@ class Context:
 
     def __init__(self, device=0, max_streams=1024, max_batch_msgs=65536, max_inflight=4,
                  ring_bytes=64 << 20, arena_samples=80_000, wake_samples_max=8_000,
-                 mode=L.DO_ALL, want_frames=False, vad_threshold=0.01):
+                 mode=L.DO_ALL, want_frames=False, vad_threshold=0.01, input_format=L.FMT_MONO16K):
         self.cfg = Config(device, max_streams, max_batch_msgs, max_inflight, ring_bytes,
                           arena_samples, wake_samples_max, mode, 1 if want_frames else 0,
-                          vad_threshold)
+                          vad_threshold, input_format, 0)
         self._h = C.c_void_p()
         check(load().ga_init(C.byref(self.cfg), C.byref(self._h)))
         self._pending = {}

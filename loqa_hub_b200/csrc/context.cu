@@ -49,12 +49,15 @@ int num_sms(int *out)
 struct StreamState {
     uint64_t wake_n = 0;     // samples in the wake-word region   (RelayStream.WakeWordSignal)
     uint64_t speech_n = 0;   // samples in the speech region      (RelayStream.SpeechAudio)
+    uint64_t n_frames = 0;   // 48 kHz input only: stereo frames consumed since the stream start
 };
 
 struct Slot {
     cudaStream_t stream = nullptr;
     cudaEvent_t done = nullptr;
+    cudaEvent_t kdone = nullptr;             // kernels of this ticket finished (48 kHz input: orders the state carry)
     ga_desc *h_desc = nullptr, *d_desc = nullptr;
+    ga_rdesc *h_rdesc = nullptr, *d_rdesc = nullptr;   // 48 kHz input only
     ga_result *h_res = nullptr, *d_res = nullptr;
     ga_frame *h_frames = nullptr, *d_frames = nullptr;
     uint64_t ticket = 0;
@@ -69,11 +72,15 @@ struct ga_ctx {
     ga_config cfg;
     uint8_t *h_ring = nullptr, *d_ring = nullptr;
     float *d_arena = nullptr;
+    uint8_t *d_hist = nullptr;                 // 48 kHz input: last 47 raw frames per stream (192 B each)
+    std::vector<uint64_t> batch_stamp;         // 48 kHz input: ticket that last touched a stream ...
+    std::vector<uint32_t> batch_last;          // ... and the index of that stream's latest message in it
     uint64_t frames_cap = 0;
     std::atomic<uint64_t> ring_head{0}, ring_tail{0};
     std::vector<ga::StreamState> streams;
     std::vector<ga::Slot> slots;
     uint64_t next_ticket = 1, oldest_ticket = 1;
+    cudaEvent_t prev_kdone = nullptr;
     std::mutex mu;   // guards submit/wait/arbitrate bookkeeping (not the ring reserve path)
     // scratch for ga_arbitrate
     cudaStream_t aux = nullptr;
@@ -94,8 +101,11 @@ static void destroy(ga_ctx *c)
     for (auto &s : c->slots) {
         if (s.stream) cudaStreamSynchronize(s.stream);
         if (s.done) cudaEventDestroy(s.done);
+        if (s.kdone) cudaEventDestroy(s.kdone);
         if (s.h_desc) cudaFreeHost(s.h_desc);
         if (s.d_desc) cudaFree(s.d_desc);
+        if (s.h_rdesc) cudaFreeHost(s.h_rdesc);
+        if (s.d_rdesc) cudaFree(s.d_rdesc);
         if (s.h_res) cudaFreeHost(s.h_res);
         if (s.d_res) cudaFree(s.d_res);
         if (s.h_frames) cudaFreeHost(s.h_frames);
@@ -106,6 +116,7 @@ static void destroy(ga_ctx *c)
     if (c->h_ring) cudaFreeHost(c->h_ring);
     if (c->d_ring) cudaFree(c->d_ring);
     if (c->d_arena) cudaFree(c->d_arena);
+    if (c->d_hist) cudaFree(c->d_hist);
     delete c;
 }
 
@@ -127,10 +138,10 @@ using namespace ga;
 extern "C" const char *ga_last_error(void) { return t_err; }
 extern "C" uint64_t ga_launch_count(void) { return g_launches.load(); }
 extern "C" int ga_abi_version(void) { return GA_ABI_VERSION; }
-extern "C" void ga_abi_sizes(uint32_t out[5])
+extern "C" void ga_abi_sizes(uint32_t out[6])
 {
     out[0] = sizeof(ga_result); out[1] = sizeof(ga_frame); out[2] = sizeof(ga_desc);
-    out[3] = sizeof(ga_msg); out[4] = sizeof(ga_config);
+    out[3] = sizeof(ga_msg); out[4] = sizeof(ga_config); out[5] = sizeof(ga_rdesc);
 }
 extern "C" int ga_device_count(void)
 {
@@ -143,6 +154,8 @@ static_assert(sizeof(ga_result) == 64, "ga_result layout");
 static_assert(sizeof(ga_frame) == 32, "ga_frame layout");
 static_assert(sizeof(ga_desc) == 32, "ga_desc layout");
 static_assert(sizeof(ga_msg) == 24, "ga_msg layout");
+static_assert(sizeof(ga_rdesc) == 64, "ga_rdesc layout");
+static_assert(sizeof(ga_config) == 64, "ga_config layout");
 
 extern "C" int ga_init(const ga_config *cfg, ga_ctx **out)
 {
@@ -157,6 +170,11 @@ extern "C" int ga_init(const ga_config *cfg, ga_ctx **out)
         (cfg->arena_samples == 0 || (cfg->arena_samples & 3u) || (cfg->wake_samples_max & 3u) ||
          cfg->wake_samples_max >= cfg->arena_samples)) {
         set_error("ga_init: arena_samples / wake_samples_max must be multiples of 4 with wake < arena");
+        return GA_ERR_ARG;
+    }
+    if (cfg->input_format > GA_FMT_STEREO48K ||
+        (cfg->input_format == GA_FMT_STEREO48K && !(cfg->mode & GA_DO_CONVERT))) {
+        set_error("ga_init: bad input_format (48 kHz stereo input needs GA_DO_CONVERT)");
         return GA_ERR_ARG;
     }
     int ndev = 0;
@@ -180,9 +198,15 @@ extern "C" int ga_init(const ga_config *cfg, ga_ctx **out)
         const uint64_t arena = static_cast<uint64_t>(cfg->max_streams) * cfg->arena_samples;
         GA_ALLOC_TRY(cudaMalloc(reinterpret_cast<void **>(&c->d_arena), (arena + 4) * sizeof(float)));
     }
+    const bool fmt48 = cfg->input_format == GA_FMT_STEREO48K;
+    if (fmt48) {
+        GA_ALLOC_TRY(cudaMalloc(reinterpret_cast<void **>(&c->d_hist), static_cast<size_t>(cfg->max_streams) * 192));
+        GA_ALLOC_TRY(cudaMemset(c->d_hist, 0, static_cast<size_t>(cfg->max_streams) * 192));
+    }
     try {
         c->streams.resize(cfg->max_streams);
         c->slots.resize(c->cfg.max_inflight);
+        if (fmt48) { c->batch_stamp.assign(cfg->max_streams, 0); c->batch_last.assign(cfg->max_streams, 0); }
     } catch (...) {
         set_error("ga_init: out of host memory");
         destroy(c);
@@ -192,8 +216,13 @@ extern "C" int ga_init(const ga_config *cfg, ga_ctx **out)
     for (auto &s : c->slots) {
         GA_ALLOC_TRY(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
         GA_ALLOC_TRY(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+        GA_ALLOC_TRY(cudaEventCreateWithFlags(&s.kdone, cudaEventDisableTiming));
         GA_ALLOC_TRY(cudaHostAlloc(reinterpret_cast<void **>(&s.h_desc), sizeof(ga_desc) * cfg->max_batch_msgs, cudaHostAllocDefault));
         GA_ALLOC_TRY(cudaMalloc(reinterpret_cast<void **>(&s.d_desc), sizeof(ga_desc) * cfg->max_batch_msgs));
+        if (fmt48) {
+            GA_ALLOC_TRY(cudaHostAlloc(reinterpret_cast<void **>(&s.h_rdesc), sizeof(ga_rdesc) * cfg->max_batch_msgs, cudaHostAllocDefault));
+            GA_ALLOC_TRY(cudaMalloc(reinterpret_cast<void **>(&s.d_rdesc), sizeof(ga_rdesc) * cfg->max_batch_msgs));
+        }
         GA_ALLOC_TRY(cudaHostAlloc(reinterpret_cast<void **>(&s.h_res), sizeof(ga_result) * cfg->max_batch_msgs, cudaHostAllocDefault));
         GA_ALLOC_TRY(cudaMalloc(reinterpret_cast<void **>(&s.d_res), sizeof(ga_result) * cfg->max_batch_msgs));
         if (c->frames_cap) {
@@ -267,6 +296,9 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
     ga_desc *descs = slot->h_desc;
     StreamState *streams = ctx->streams.data();
     const uint32_t max_streams = ctx->cfg.max_streams;
+    const bool fmt48 = ctx->cfg.input_format == GA_FMT_STEREO48K;
+    ga_rdesc *rdescs = slot->h_rdesc;
+    const uint64_t stamp = ctx->next_ticket;      // marks streams already seen in THIS batch
     for (; i < n; i++) {
         const ga_msg &m = msgs[i];
         const uint64_t need = (static_cast<uint64_t>(m.nbytes) + 15u) & ~15ull;
@@ -279,7 +311,38 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
         }
         StreamState &st = streams[m.stream_id];
         if (m.flags & GA_MSG_FIRST) { resets.push_back({st}); st = StreamState(); }
-        const uint64_t ns = m.nbytes >> 1;
+        uint64_t ns = m.nbytes >> 1;
+        if (fmt48) {
+            // 48 kHz stereo: the message yields one output per input frame index 3M+2 it contains
+            if (m.nbytes > GA_RS_MAX_MSG_BYTES) {
+                if (m.flags & GA_MSG_FIRST) { st = resets.back().before; resets.pop_back(); }
+                set_error("ga_submit: msg %u: 48 kHz chunks are limited to %u bytes", i, GA_RS_MAX_MSG_BYTES);
+                err = GA_ERR_ARG;
+                break;
+            }
+            const uint64_t nfr = m.nbytes >> 2, n0 = st.n_frames, n1 = n0 + nfr, mf = n0 / 3;
+            ns = (n1 >= 3 * mf + 3) ? (n1 - 3 * mf - 3) / 3 + 1 : 0;
+            ga_rdesc &r = rdescs[i];
+            r.in_off = phys; r.nbytes = m.nbytes; r.stream_id = m.stream_id; r.n0 = n0;
+            r.flags = m.flags | GA_RS_SAVE_HIST; r.hist_off = 0; r.hist_kind = GA_HIST_ZERO;
+            r.reserved[0] = r.reserved[1] = r.reserved[2] = 0;
+            if (ctx->batch_stamp[m.stream_id] == stamp) {
+                // the stream's previous chunk is in this very batch: take the history from the slab
+                ga_rdesc &prev = rdescs[ctx->batch_last[m.stream_id]];
+                const uint64_t pfr = prev.nbytes >> 2;
+                if (pfr < 47) {
+                    if (m.flags & GA_MSG_FIRST) { st = resets.back().before; resets.pop_back(); }
+                    set_error("ga_submit: msg %u: its stream's previous chunk in this batch has %llu < 47 frames; "
+                              "submit short 48 kHz chunks in separate batches", i, (unsigned long long)pfr);
+                    err = GA_ERR_ARG;
+                    break;
+                }
+                if (!(m.flags & GA_MSG_FIRST)) { r.hist_kind = GA_HIST_SLAB; r.hist_off = prev.in_off + (pfr - 47) * 4; }
+                prev.flags &= ~GA_RS_SAVE_HIST;             // only the stream's last chunk of the batch saves
+            } else if (n0 != 0) {
+                r.hist_kind = GA_HIST_STATE;
+            }
+        }
         const bool is_wake = (m.flags & GA_MSG_WAKE) != 0;
         uint64_t &cursor = is_wake ? st.wake_n : st.speech_n;   // audio_service.go:965 / :1002 append
         ga_desc &d = descs[i];
@@ -300,6 +363,13 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
             d.out_off = static_cast<uint64_t>(m.stream_id) * arena + region + cursor;
         }
         cursor += ns;
+        if (fmt48) {
+            rdescs[i].out_off = d.out_off;
+            rdescs[i].frame_off = d.frame_off;
+            st.n_frames += m.nbytes >> 2;
+            ctx->batch_stamp[m.stream_id] = stamp;
+            ctx->batch_last[m.stream_id] = i;
+        }
         frames += (ns + GA_FRAME_SAMPLES - 1) / GA_FRAME_SAMPLES;
         const uint64_t end = m.ring_offset + need;
         if (end > release_to) release_to = end;
@@ -324,7 +394,15 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
         while (i-- > 0) {
             const ga_msg &m = msgs[i];
             StreamState &st = streams[m.stream_id];
-            ((m.flags & GA_MSG_WAKE) ? st.wake_n : st.speech_n) -= m.nbytes >> 1;
+            uint64_t ns = m.nbytes >> 1;
+            if (fmt48) {
+                const uint64_t nfr = m.nbytes >> 2;
+                st.n_frames -= nfr;
+                const uint64_t n0 = st.n_frames, n1 = n0 + nfr, mf = n0 / 3;
+                ns = (n1 >= 3 * mf + 3) ? (n1 - 3 * mf - 3) / 3 + 1 : 0;
+                ctx->batch_stamp[m.stream_id] = 0;
+            }
+            ((m.flags & GA_MSG_WAKE) ? st.wake_n : st.speech_n) -= ns;
             if (m.flags & GA_MSG_FIRST) { st = resets.back().before; resets.pop_back(); }
         }
         return err;
@@ -342,9 +420,29 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
         GA_CUDA_TRY(cudaMemcpyAsync(ctx->d_ring + runs[r].lo, ctx->h_ring + runs[r].lo, runs[r].hi - runs[r].lo, cudaMemcpyHostToDevice, s));
     if (n) {
         GA_CUDA_TRY(cudaMemcpyAsync(slot->d_desc, slot->h_desc, sizeof(ga_desc) * n, cudaMemcpyHostToDevice, s));
-        rc = ga_k_ingest(ctx->d_ring, slot->d_desc, n, ctx->d_arena, slot->d_res,
-                         ctx->frames_cap ? slot->d_frames : nullptr, ctx->cfg.mode, ctx->cfg.vad_threshold, s);
-        if (rc) return rc;
+        if (!fmt48) {
+            rc = ga_k_ingest(ctx->d_ring, slot->d_desc, n, ctx->d_arena, slot->d_res,
+                             ctx->frames_cap ? slot->d_frames : nullptr, ctx->cfg.mode, ctx->cfg.vad_threshold, s);
+            if (rc) return rc;
+        } else {
+            // fingerprint of the received bytes first (writes whole records), then the decimator
+            // fills the statistics of the resampled samples into the same records
+            GA_CUDA_TRY(cudaMemcpyAsync(slot->d_rdesc, slot->h_rdesc, sizeof(ga_rdesc) * n, cudaMemcpyHostToDevice, s));
+            if (ctx->cfg.mode & GA_DO_SHA256) {
+                rc = ga_k_ingest(ctx->d_ring, slot->d_desc, n, nullptr, slot->d_res, nullptr, GA_DO_SHA256, ctx->cfg.vad_threshold, s);
+                if (rc) return rc;
+            } else {
+                GA_CUDA_TRY(cudaMemsetAsync(slot->d_res, 0, sizeof(ga_result) * n, s));
+            }
+            // tickets run on their own CUDA streams; the per-stream history carried in d_hist makes
+            // the decimator launches of consecutive tickets dependent, so chain them
+            if (ctx->prev_kdone) GA_CUDA_TRY(cudaStreamWaitEvent(s, ctx->prev_kdone, 0));
+            rc = ga_k_resample48(ctx->d_ring, slot->d_rdesc, n, ctx->d_hist, ctx->d_arena, slot->d_res,
+                                 ctx->frames_cap ? slot->d_frames : nullptr, ctx->cfg.vad_threshold, s);
+            if (rc) return rc;
+            GA_CUDA_TRY(cudaEventRecord(slot->kdone, s));
+            ctx->prev_kdone = slot->kdone;
+        }
         GA_CUDA_TRY(cudaMemcpyAsync(slot->h_res, slot->d_res, sizeof(ga_result) * n, cudaMemcpyDeviceToHost, s));
         if (ctx->frames_cap && frames)
             GA_CUDA_TRY(cudaMemcpyAsync(slot->h_frames, slot->d_frames, sizeof(ga_frame) * frames, cudaMemcpyDeviceToHost, s));
@@ -723,6 +821,41 @@ extern "C" int ga_synth_fill_batch_device_map(void *d_pcm, uint64_t seed, const 
     synth_batch_map_kernel<<<sms * 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(
         static_cast<int16_t *>(d_pcm), seed, d_group, d_relay, n_streams, n_msgs, msg_samples);
     GA_CHECK_LAUNCH("synth_batch_map_kernel");
+    return GA_OK;
+}
+
+// 48 kHz stereo view of the same relay PCM: 3x zero-order hold, R = L - (L >> 3)
+__global__ void synth_batch48_map_kernel(uint32_t *pcm, uint64_t seed, const uint32_t *__restrict__ group,
+                                         const uint32_t *__restrict__ relay, uint32_t n_streams,
+                                         uint32_t n_msgs, uint32_t msg_frames)
+{
+    const uint64_t total = static_cast<uint64_t>(n_msgs) * n_streams * msg_frames;
+    const uint32_t utt = (n_msgs * msg_frames + 2) / 3;
+    for (uint64_t i = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<uint64_t>(gridDim.x) * blockDim.x) {
+        const uint32_t k = static_cast<uint32_t>(i % msg_frames);
+        const uint64_t ms = i / msg_frames;
+        const uint32_t s = static_cast<uint32_t>(ms % n_streams);
+        const uint32_t m = static_cast<uint32_t>(ms / n_streams);
+        const int32_t l = synth::sample(seed, group[s], relay[s], (m * msg_frames + k) / 3, utt);
+        const int32_t r = l - (l >> 3);
+        pcm[i] = (static_cast<uint32_t>(l) & 0xFFFFu) | (static_cast<uint32_t>(r) << 16);
+    }
+}
+
+extern "C" int ga_synth_fill_batch48_device_map(void *d_pcm, uint64_t seed, const uint32_t *d_group,
+                                                const uint32_t *d_relay, uint32_t n_streams,
+                                                uint32_t n_msgs, uint32_t msg_frames, void *stream)
+{
+    if (!d_pcm || !d_group || !d_relay) { set_error("ga_synth_fill_batch48_device_map: bad argument"); return GA_ERR_ARG; }
+    const uint64_t total = static_cast<uint64_t>(n_msgs) * n_streams * msg_frames;
+    if (total == 0) return GA_OK;
+    int sms = 0;
+    int rc = num_sms(&sms);
+    if (rc) return rc;
+    synth_batch48_map_kernel<<<sms * 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<uint32_t *>(d_pcm), seed, d_group, d_relay, n_streams, n_msgs, msg_frames);
+    GA_CHECK_LAUNCH("synth_batch48_map_kernel");
     return GA_OK;
 }
 

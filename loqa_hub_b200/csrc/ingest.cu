@@ -100,7 +100,6 @@ ingest_kernel(const IngestParams p)
     using L = TileSmem<CH, STAGES>;
     constexpr bool kCoop = (MODE & GA_DO_CONVERT) != 0 && COOP == 1;      // cooperative store pass
     constexpr bool kLaneStore = (MODE & GA_DO_CONVERT) != 0 && COOP == 0; // lane stores its own samples
-    constexpr bool kConvert = (MODE & GA_DO_CONVERT) != 0;
     constexpr bool kFeat = (MODE & GA_DO_FEATURES) != 0;
     constexpr bool kSha = (MODE & GA_DO_SHA256) != 0;
     constexpr uint32_t FULL = 0xffffffffu;

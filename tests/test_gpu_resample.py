@@ -1,0 +1,131 @@
+"""48 kHz stereo -> 16 kHz mono decimator (BASELINE configs[3]) through the C ABI against the
+oracle's ora_resample_48k_stereo.  The filter is new spec (the reference ignores
+AudioChunk.SampleRate, internal/grpc/audio_service.go:926-1043), so the oracle is the definition
+("parity unpinned" at the reference level); what IS pinned is A1's conversion inside it and the
+statistics (calculateSignalStrength, :818-852) of the resampled samples.  Fixed tap order +
+explicit FMAs make the output reproducible, so everything here is compared bit for bit."""
+import struct
+
+import numpy as np
+import pytest
+
+from loqa_hub_b200 import _lib as L
+from loqa_hub_b200 import api, synth
+from oracle import oracle as ora
+
+pytestmark = pytest.mark.gpu
+
+
+def bits(x):
+    return np.asarray(x, dtype=np.float32).view(np.uint32)
+
+
+def stereo48(group, relay, n_frames):
+    """SURVEY §8d cfg4 input: 3x zero-order hold of the relay's 16 kHz view, R = L - (L >> 3)."""
+    x = synth.relay_view(group, relay, (n_frames + 2) // 3).astype(np.int32)
+    left = np.repeat(x, 3)[:n_frames]
+    right = left - (left >> 3)
+    return np.stack([left, right], axis=1).astype("<i2")
+
+
+@pytest.fixture(scope="module")
+def ctx48():
+    import __graft_entry__ as entry
+    entry.build()
+    c = api.Context(device=0, max_streams=64, max_batch_msgs=8192, max_inflight=4, ring_bytes=64 << 20,
+                    arena_samples=40_000, wake_samples_max=8_000, mode=L.DO_ALL, want_frames=True,
+                    input_format=L.FMT_STEREO48K)
+    yield c
+    c.close()
+
+
+def oracle_stream(chunks):
+    r, parts = ora.Resampler(), []
+    for c in chunks:
+        parts.append(r.process(c))
+    return parts
+
+
+def check(res, frames, chunks, parts):
+    fpos = 0
+    for i, (data, y) in enumerate(zip(chunks, parts)):
+        assert res["digest"][i].tobytes() == ora.sha256(data)          # fingerprint of the RECEIVED bytes
+        rms, st = ora.signal_strength(y)
+        assert res["n_samples"][i] == y.size
+        assert struct.pack("<d", res["sumsq"][i]) == struct.pack("<d", st.sumsq)
+        assert struct.pack("<d", res["rms"][i]) == struct.pack("<d", rms)
+        assert res["nonzero"][i] == st.nonzero and bits(res["peak"][i]) == bits(st.peak)
+        of = ora.frame_features(y, L.FRAME_SAMPLES, 0.01)
+        for a, b in zip(frames[fpos:fpos + len(of)], of):
+            assert (a["sumsq"], a["rms"], a["n_samples"], a["nonzero"], a["vad"]) == \
+                   (b["sumsq"], b["rms"], b["n_samples"], b["nonzero"], b["vad"])
+            assert bits(a["peak"]) == bits(b["peak"])
+        fpos += len(of)
+    assert fpos == len(frames)
+
+
+def test_cfg4_streams_whole_utterance_in_one_batch(ctx48):
+    """8 streams x 25 chunks of 3,840 B (20 ms of 48 kHz stereo), time-major, ONE submit: every
+    chunk after the first takes its 47-frame history from its predecessor in the slab."""
+    n_streams, n_msgs, fr = 8, 25, 960
+    pcm = [stereo48(3 + s // 4, s % 4, n_msgs * fr) for s in range(n_streams)]
+    chunks, sid, flags = [], [], []
+    for m in range(n_msgs):
+        for s in range(n_streams):
+            chunks.append(pcm[s][m * fr:(m + 1) * fr].tobytes())
+            sid.append(s)
+            flags.append((L.MSG_FIRST if m == 0 else 0) | (L.MSG_WAKE if m < 15 else 0))
+    res, frames = ctx48.ingest(chunks, np.array(sid, np.uint32), np.array(flags, np.uint32))
+    for s in range(n_streams):
+        mine = [i for i in range(len(chunks)) if sid[i] == s]
+        parts = oracle_stream([chunks[i] for i in mine])
+        got = ctx48.fetch_samples(s)
+        assert np.array_equal(bits(got), bits(np.concatenate(parts))), s
+        assert ctx48.stream_info(s) == (n_msgs * 320, 15 * 320)
+        check(res[mine], frames[mine], [chunks[i] for i in mine], parts)     # 1 frame per 320-sample message
+    # arbitration on the resampled wake-word buffers: relay 0 of each group is the loudest
+    winner, scores, _ = ctx48.arbitrate(np.array([0, 4, 8], np.uint32), np.arange(8, dtype=np.uint32))
+    assert list(winner) == [0, 4]
+    y0 = np.concatenate(oracle_stream([pcm[0][m * fr:(m + 1) * fr].tobytes() for m in range(15)]))
+    assert scores[0] == ora.signal_strength(y0)[0]
+
+
+def test_history_carries_across_batches_and_odd_chunk_sizes(ctx48):
+    """Ragged chunking (frame counts that are not multiples of 3, short chunks, a trailing partial
+    frame), one chunk per submit so the history comes from the saved per-stream state, mixed with
+    batches that hold several chunks of the stream."""
+    rng = np.random.default_rng(5)
+    total = 6000
+    pcm = np.stack([rng.integers(-30000, 30000, total), rng.integers(-30000, 30000, total)], axis=1).astype("<i2")
+    raw = pcm.tobytes()
+    sizes = [4 * 7, 4 * 1, 3840, 4 * 50, 4 * 2 + 3, 4 * 959, 4 * 100, 4 * 47, 3840, 3840, 4 * 333]
+    chunks, pos = [], 0
+    for n in sizes:
+        chunks.append(raw[pos:pos + n]); pos += n - (n % 4)        # a partial frame is dropped, not carried
+    parts = oracle_stream(chunks)
+    plan = [[0], [1], [2], [3], [4], [5, 6], [7], [8, 9, 10]]       # chunks per submit (predecessors >= 47 frames)
+    out_res = []
+    for k, group in enumerate(plan):
+        fl = [L.MSG_FIRST if (k == 0 and j == 0) else 0 for j in range(len(group))]
+        res, frames = ctx48.ingest([chunks[i] for i in group], np.full(len(group), 9, np.uint32), np.array(fl, np.uint32))
+        out_res.append(res)
+    res = np.concatenate(out_res)
+    got = ctx48.fetch_samples(9)
+    assert np.array_equal(bits(got), bits(np.concatenate(parts)))
+    for i, (data, y) in enumerate(zip(chunks, parts)):
+        assert res["digest"][i].tobytes() == ora.sha256(data)
+        assert res["n_samples"][i] == y.size
+        assert struct.pack("<d", res["rms"][i]) == struct.pack("<d", ora.signal_strength(y)[0])
+
+
+def test_48k_boundary_rules(ctx48):
+    with pytest.raises(L.GpuAudioError) as e:
+        ctx48.ingest([b"\x00" * 3844], [1], [L.MSG_FIRST])
+    assert e.value.code == L.GA_ERR_ARG and "3840" in str(e.value)
+    before = ctx48.stream_info(2)
+    with pytest.raises(L.GpuAudioError) as e:                       # predecessor in the same batch too short
+        ctx48.ingest([b"\x01" * 40, b"\x01" * 400], [2, 2], [L.MSG_FIRST, 0])
+    assert e.value.code == L.GA_ERR_ARG and "47 frames" in str(e.value)
+    assert ctx48.stream_info(2) == before                           # the failed submit left no trace
+    res, _ = ctx48.ingest([b"\x01" * 400], [2], [L.MSG_FIRST])
+    assert res["n_samples"][0] == 33
