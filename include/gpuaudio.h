@@ -59,6 +59,8 @@ enum {
 #define GA_DO_FEATURES  0x02u /* per-message (+ optional per-frame) energy statistics    */
 #define GA_DO_SHA256    0x04u /* per-message SHA-256 fingerprint of the received bytes   */
 #define GA_DO_ALL       0x07u
+#define GA_DO_UTTERANCE 0x08u /* context layer: also keep a running SHA-256 per stream over all
+                                 received bytes of the utterance (ga_utterance_digest)       */
 
 #define GA_FRAME_SAMPLES 320u /* 20 ms at 16 kHz                  */
 
@@ -141,6 +143,32 @@ int ga_k_signal_strength(const float *d_samples, const uint64_t *d_wake_off, con
  * exchanged records).  Same rules as above. */
 int ga_k_select(const double *d_scores, const uint8_t *d_status_in, const uint32_t *d_seg_offsets,
                 uint32_t n_windows, uint32_t *d_winner, uint8_t *d_status_out, void *stream);
+
+/* Running SHA-256 of one stream, 128 bytes: midstate, bytes hashed so far, and the not yet
+ * compressed tail.  A fresh state holds the FIPS 180-4 initial hash value (ga_k_sha256_reset). */
+typedef struct ga_sha_state {
+    uint32_t h[8];
+    uint64_t total_len;
+    uint32_t tail_len;    /* 0..63 */
+    uint32_t reserved;
+    uint8_t  tail[64];
+    uint8_t  pad[16];
+} ga_sha_state;
+
+/* Per-utterance fingerprint (the "audio_hash" of a voice event: API.md:170, hook
+ * events/voice_event.go:84-88; chunks arrive through StreamAudio, audio_service.go:939-1005).
+ * Lane r walks the linked list of messages  i = run_first[r], next[i], next[next[i]] …
+ * (UINT32_MAX ends it) — all of ONE stream, in arrival order — and continues that stream's
+ * running SHA-256 in d_state[desc[i].stream_id]; a message flagged GA_MSG_FIRST restarts it.
+ * Launches that touch the same stream must be ordered by the caller. */
+int ga_k_sha256_chain(const void *d_pcm, const ga_desc *d_desc, const uint32_t *d_run_first,
+                      const uint32_t *d_next, uint32_t n_runs, ga_sha_state *d_state, void *stream);
+/* Digest of everything hashed so far for n streams (d_stream_ids NULL = streams 0..n-1), computed
+ * on a copy of each state: d_digests[32*n], d_lengths[n] (nullable) = bytes hashed. */
+int ga_k_sha256_final(const ga_sha_state *d_state, const uint32_t *d_stream_ids, uint32_t n,
+                      uint8_t *d_digests, uint64_t *d_lengths, void *stream);
+/* (Re)initialise n states starting at d_state to the empty-message state. */
+int ga_k_sha256_reset(ga_sha_state *d_state, uint32_t n, void *stream);
 
 /* Descriptor of one 48 kHz interleaved-stereo int16 message for ga_k_resample48, 64 bytes. */
 #define GA_HIST_ZERO   0u   /* stream start: the 47 frames before the message are silence          */
@@ -273,6 +301,10 @@ int ga_wait_view(ga_ctx *ctx, uint64_t ticket, const ga_result **results, const 
 int ga_fetch_samples(ga_ctx *ctx, uint32_t stream_id, uint64_t first, uint64_t n, float *out);
 int ga_stream_info(ga_ctx *ctx, uint32_t stream_id, uint64_t *n_samples, uint64_t *wake_samples);
 int ga_stream_reset(ga_ctx *ctx, uint32_t stream_id);
+/* Contexts with GA_DO_UTTERANCE: SHA-256 of all bytes the stream has received since its last
+ * GA_MSG_FIRST (in arrival order), as of the last submitted batch; total_bytes may be NULL.
+ * Typically read when the chunk flagged IsEndOfSpeech (audio_service.go:1008) has been waited. */
+int ga_utterance_digest(ga_ctx *ctx, uint32_t stream_id, uint8_t digest[32], uint64_t *total_bytes);
 /* Device address of the f32 sample arena (stream s starts at s * arena_samples; its wake-word
  * region first, its speech region at + wake_samples_max).  For harnesses that run the
  * ga_k_* arbitration sequence (e.g. with an exchange step between shards) on the context's
@@ -330,8 +362,9 @@ int ga_synth_fill_batch_host(void *pcm, uint64_t seed, uint32_t group_base, uint
 /* Introspection for harnesses. */
 uint64_t ga_launch_count(void);            /* kernels launched by this library so far */
 int      ga_abi_version(void);
-/* sizes of {ga_result, ga_frame, ga_desc, ga_msg, ga_config, ga_rdesc} for binding self-checks */
-void     ga_abi_sizes(uint32_t out[6]);
+/* sizes of {ga_result, ga_frame, ga_desc, ga_msg, ga_config, ga_rdesc, ga_sha_state} for binding
+ * self-checks */
+void     ga_abi_sizes(uint32_t out[7]);
 int      ga_device_count(void);
 
 #ifdef __cplusplus

@@ -17,6 +17,7 @@ GA_ERR_OVERFLOW, GA_ERR_STATE, GA_ERR_COMM = -5, -6, -7
 RELAY_CONNECTED, RELAY_CONTENDING, RELAY_WINNER, RELAY_CANCELLED = 0, 1, 2, 3
 MSG_WAKE, MSG_EOS, MSG_FIRST = 1, 2, 4
 DO_CONVERT, DO_FEATURES, DO_SHA256, DO_ALL = 1, 2, 4, 7
+DO_UTTERANCE = 8
 FRAME_SAMPLES = 320
 NO_WINNER = 0xFFFFFFFF
 
@@ -50,6 +51,10 @@ class Config(C.Structure):
 _vp, _u32, _u64, _i32, _sz = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int, C.c_size_t
 SYMBOLS = {
     "ga_k_ingest": (_i32, [_vp, _vp, _u32, _vp, _vp, _vp, _u32, C.c_double, _vp]),
+    "ga_k_sha256_chain": (_i32, [_vp, _vp, _vp, _vp, _u32, _vp, _vp]),
+    "ga_k_sha256_final": (_i32, [_vp, _vp, _u32, _vp, _vp, _vp]),
+    "ga_k_sha256_reset": (_i32, [_vp, _u32, _vp]),
+    "ga_utterance_digest": (_i32, [_vp, _u32, _vp, C.POINTER(_u64)]),
     "ga_k_resample48": (_i32, [_vp, _vp, _u32, _vp, _vp, _vp, _vp, C.c_double, _vp]),
     "ga_k_arbitrate": (_i32, [_vp, _vp, _vp, _vp, _vp, _u32, _u32, _vp, _vp, _vp, _vp]),
     "ga_k_arbitrate_noalloc": (_i32, [_vp, _vp, _vp, _vp, _vp, _u32, _u32, _vp, _vp, _vp]),
@@ -79,7 +84,7 @@ SYMBOLS = {
     "ga_synth_fill_batch_host": (_i32, [_vp, _u64, _u32, _u32, _u32, _u32, _u32, _u32]),
     "ga_launch_count": (_u64, []),
     "ga_abi_version": (_i32, []),
-    "ga_abi_sizes": (None, [C.POINTER(_u32 * 6)]),
+    "ga_abi_sizes": (None, [C.POINTER(_u32 * 7)]),
     "ga_device_count": (_i32, []),
 }
 
@@ -106,10 +111,10 @@ def load():
         fn = getattr(lib, name)      # AttributeError if the .so does not export it
         fn.restype = res
         fn.argtypes = args
-    sizes = (_u32 * 6)()
+    sizes = (_u32 * 7)()
     lib.ga_abi_sizes(C.byref(sizes))
     want = [RESULT_DTYPE.itemsize, FRAME_DTYPE.itemsize, DESC_DTYPE.itemsize, MSG_DTYPE.itemsize,
-            C.sizeof(Config), RDESC_DTYPE.itemsize]
+            C.sizeof(Config), RDESC_DTYPE.itemsize, 128]
     if list(sizes) != want:
         raise ImportError("libgpuaudio ABI struct sizes %s != binding %s" % (list(sizes), want))
     _lib = lib

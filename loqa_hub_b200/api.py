@@ -38,6 +38,18 @@ def k_ingest(d_pcm, d_desc, n_msgs, d_samples, d_results, d_frames=0, mode=L.DO_
                              mode, vad_threshold, stream or None))
 
 
+def k_sha256_chain(d_pcm, d_desc, d_run_first, d_next, n_runs, d_state, stream=0):
+    check(load().ga_k_sha256_chain(d_pcm, d_desc, d_run_first, d_next, n_runs, d_state, stream or None))
+
+
+def k_sha256_final(d_state, d_stream_ids, n, d_digests, d_lengths=0, stream=0):
+    check(load().ga_k_sha256_final(d_state, d_stream_ids or None, n, d_digests, d_lengths or None, stream or None))
+
+
+def k_sha256_reset(d_state, n, stream=0):
+    check(load().ga_k_sha256_reset(d_state, n, stream or None))
+
+
 def k_resample48(d_pcm, d_rdesc, n_msgs, d_hist_state, d_samples, d_results, d_frames=0,
                  vad_threshold=0.01, stream=0):
     check(load().ga_k_resample48(d_pcm, d_rdesc, n_msgs, d_hist_state or None, d_samples, d_results,
@@ -198,6 +210,13 @@ class Context:
         a, b = C.c_uint64(), C.c_uint64()
         check(load().ga_stream_info(self._h, stream_id, C.byref(a), C.byref(b)))
         return a.value, b.value
+
+    def utterance_digest(self, stream_id):
+        """(digest bytes, bytes hashed) of the stream's running per-utterance SHA-256."""
+        out = np.zeros(32, dtype=np.uint8)
+        n = C.c_uint64()
+        check(load().ga_utterance_digest(self._h, stream_id, ptr(out), C.byref(n)))
+        return out.tobytes(), n.value
 
     def stream_reset(self, stream_id):
         check(load().ga_stream_reset(self._h, stream_id))

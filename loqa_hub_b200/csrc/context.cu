@@ -58,6 +58,7 @@ struct Slot {
     cudaEvent_t kdone = nullptr;             // kernels of this ticket finished (48 kHz input: orders the state carry)
     ga_desc *h_desc = nullptr, *d_desc = nullptr;
     ga_rdesc *h_rdesc = nullptr, *d_rdesc = nullptr;   // 48 kHz input only
+    uint32_t *h_link = nullptr, *d_link = nullptr;     // GA_DO_UTTERANCE: next[n] then run_first[n]
     ga_result *h_res = nullptr, *d_res = nullptr;
     ga_frame *h_frames = nullptr, *d_frames = nullptr;
     uint64_t ticket = 0;
@@ -73,6 +74,7 @@ struct ga_ctx {
     uint8_t *h_ring = nullptr, *d_ring = nullptr;
     float *d_arena = nullptr;
     uint8_t *d_hist = nullptr;                 // 48 kHz input: last 47 raw frames per stream (192 B each)
+    ga_sha_state *d_sha = nullptr;             // GA_DO_UTTERANCE: running digest per stream
     std::vector<uint64_t> batch_stamp;         // 48 kHz input: ticket that last touched a stream ...
     std::vector<uint32_t> batch_last;          // ... and the index of that stream's latest message in it
     uint64_t frames_cap = 0;
@@ -104,6 +106,8 @@ static void destroy(ga_ctx *c)
         if (s.kdone) cudaEventDestroy(s.kdone);
         if (s.h_desc) cudaFreeHost(s.h_desc);
         if (s.d_desc) cudaFree(s.d_desc);
+        if (s.h_link) cudaFreeHost(s.h_link);
+        if (s.d_link) cudaFree(s.d_link);
         if (s.h_rdesc) cudaFreeHost(s.h_rdesc);
         if (s.d_rdesc) cudaFree(s.d_rdesc);
         if (s.h_res) cudaFreeHost(s.h_res);
@@ -117,6 +121,7 @@ static void destroy(ga_ctx *c)
     if (c->d_ring) cudaFree(c->d_ring);
     if (c->d_arena) cudaFree(c->d_arena);
     if (c->d_hist) cudaFree(c->d_hist);
+    if (c->d_sha) cudaFree(c->d_sha);
     delete c;
 }
 
@@ -138,10 +143,11 @@ using namespace ga;
 extern "C" const char *ga_last_error(void) { return t_err; }
 extern "C" uint64_t ga_launch_count(void) { return g_launches.load(); }
 extern "C" int ga_abi_version(void) { return GA_ABI_VERSION; }
-extern "C" void ga_abi_sizes(uint32_t out[6])
+extern "C" void ga_abi_sizes(uint32_t out[7])
 {
     out[0] = sizeof(ga_result); out[1] = sizeof(ga_frame); out[2] = sizeof(ga_desc);
     out[3] = sizeof(ga_msg); out[4] = sizeof(ga_config); out[5] = sizeof(ga_rdesc);
+    out[6] = sizeof(ga_sha_state);
 }
 extern "C" int ga_device_count(void)
 {
@@ -156,13 +162,14 @@ static_assert(sizeof(ga_desc) == 32, "ga_desc layout");
 static_assert(sizeof(ga_msg) == 24, "ga_msg layout");
 static_assert(sizeof(ga_rdesc) == 64, "ga_rdesc layout");
 static_assert(sizeof(ga_config) == 64, "ga_config layout");
+static_assert(sizeof(ga_sha_state) == 128, "ga_sha_state layout");
 
 extern "C" int ga_init(const ga_config *cfg, ga_ctx **out)
 {
     if (!cfg || !out) { set_error("ga_init: NULL argument"); return GA_ERR_ARG; }
     *out = nullptr;
     if (cfg->max_streams == 0 || cfg->max_batch_msgs == 0 || cfg->ring_bytes < 4096 ||
-        (cfg->ring_bytes & 15u) || (cfg->mode & GA_DO_ALL) == 0) {
+        (cfg->ring_bytes & 15u) || (cfg->mode & (GA_DO_ALL | GA_DO_UTTERANCE)) == 0) {
         set_error("ga_init: bad config (streams/batch/ring/mode)");
         return GA_ERR_ARG;
     }
@@ -203,10 +210,17 @@ extern "C" int ga_init(const ga_config *cfg, ga_ctx **out)
         GA_ALLOC_TRY(cudaMalloc(reinterpret_cast<void **>(&c->d_hist), static_cast<size_t>(cfg->max_streams) * 192));
         GA_ALLOC_TRY(cudaMemset(c->d_hist, 0, static_cast<size_t>(cfg->max_streams) * 192));
     }
+    const bool utter = (cfg->mode & GA_DO_UTTERANCE) != 0;
+    if (utter) {
+        GA_ALLOC_TRY(cudaMalloc(reinterpret_cast<void **>(&c->d_sha), sizeof(ga_sha_state) * cfg->max_streams));
+        GA_ALLOC_TRY(cudaMemset(c->d_sha, 0, sizeof(ga_sha_state) * cfg->max_streams));
+        if (ga_k_sha256_reset(c->d_sha, cfg->max_streams, nullptr) != GA_OK) { destroy(c); return GA_ERR_CUDA; }
+        GA_ALLOC_TRY(cudaDeviceSynchronize());
+    }
     try {
         c->streams.resize(cfg->max_streams);
         c->slots.resize(c->cfg.max_inflight);
-        if (fmt48) { c->batch_stamp.assign(cfg->max_streams, 0); c->batch_last.assign(cfg->max_streams, 0); }
+        if (fmt48 || utter) { c->batch_stamp.assign(cfg->max_streams, 0); c->batch_last.assign(cfg->max_streams, 0); }
     } catch (...) {
         set_error("ga_init: out of host memory");
         destroy(c);
@@ -219,6 +233,10 @@ extern "C" int ga_init(const ga_config *cfg, ga_ctx **out)
         GA_ALLOC_TRY(cudaEventCreateWithFlags(&s.kdone, cudaEventDisableTiming));
         GA_ALLOC_TRY(cudaHostAlloc(reinterpret_cast<void **>(&s.h_desc), sizeof(ga_desc) * cfg->max_batch_msgs, cudaHostAllocDefault));
         GA_ALLOC_TRY(cudaMalloc(reinterpret_cast<void **>(&s.d_desc), sizeof(ga_desc) * cfg->max_batch_msgs));
+        if (utter) {
+            GA_ALLOC_TRY(cudaHostAlloc(reinterpret_cast<void **>(&s.h_link), sizeof(uint32_t) * 2 * cfg->max_batch_msgs, cudaHostAllocDefault));
+            GA_ALLOC_TRY(cudaMalloc(reinterpret_cast<void **>(&s.d_link), sizeof(uint32_t) * 2 * cfg->max_batch_msgs));
+        }
         if (fmt48) {
             GA_ALLOC_TRY(cudaHostAlloc(reinterpret_cast<void **>(&s.h_rdesc), sizeof(ga_rdesc) * cfg->max_batch_msgs, cudaHostAllocDefault));
             GA_ALLOC_TRY(cudaMalloc(reinterpret_cast<void **>(&s.d_rdesc), sizeof(ga_rdesc) * cfg->max_batch_msgs));
@@ -297,6 +315,9 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
     StreamState *streams = ctx->streams.data();
     const uint32_t max_streams = ctx->cfg.max_streams;
     const bool fmt48 = ctx->cfg.input_format == GA_FMT_STEREO48K;
+    const bool utter = (ctx->cfg.mode & GA_DO_UTTERANCE) != 0;
+    uint32_t *link_next = slot->h_link, *link_first = slot->h_link ? slot->h_link + ctx->cfg.max_batch_msgs : nullptr;
+    uint32_t n_chains = 0;
     ga_rdesc *rdescs = slot->h_rdesc;
     const uint64_t stamp = ctx->next_ticket;      // marks streams already seen in THIS batch
     for (; i < n; i++) {
@@ -363,10 +384,18 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
             d.out_off = static_cast<uint64_t>(m.stream_id) * arena + region + cursor;
         }
         cursor += ns;
+        if (utter) {
+            // thread this message onto its stream's list for the running-digest kernel
+            link_next[i] = 0xffffffffu;
+            if (ctx->batch_stamp[m.stream_id] == stamp) link_next[ctx->batch_last[m.stream_id]] = i;
+            else link_first[n_chains++] = i;
+        }
         if (fmt48) {
             rdescs[i].out_off = d.out_off;
             rdescs[i].frame_off = d.frame_off;
             st.n_frames += m.nbytes >> 2;
+        }
+        if (fmt48 || utter) {
             ctx->batch_stamp[m.stream_id] = stamp;
             ctx->batch_last[m.stream_id] = i;
         }
@@ -400,8 +429,8 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
                 st.n_frames -= nfr;
                 const uint64_t n0 = st.n_frames, n1 = n0 + nfr, mf = n0 / 3;
                 ns = (n1 >= 3 * mf + 3) ? (n1 - 3 * mf - 3) / 3 + 1 : 0;
-                ctx->batch_stamp[m.stream_id] = 0;
             }
+            if (fmt48 || utter) ctx->batch_stamp[m.stream_id] = 0;
             ((m.flags & GA_MSG_WAKE) ? st.wake_n : st.speech_n) -= ns;
             if (m.flags & GA_MSG_FIRST) { st = resets.back().before; resets.pop_back(); }
         }
@@ -421,9 +450,13 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
     if (n) {
         GA_CUDA_TRY(cudaMemcpyAsync(slot->d_desc, slot->h_desc, sizeof(ga_desc) * n, cudaMemcpyHostToDevice, s));
         if (!fmt48) {
-            rc = ga_k_ingest(ctx->d_ring, slot->d_desc, n, ctx->d_arena, slot->d_res,
-                             ctx->frames_cap ? slot->d_frames : nullptr, ctx->cfg.mode, ctx->cfg.vad_threshold, s);
-            if (rc) return rc;
+            if (ctx->cfg.mode & GA_DO_ALL) {
+                rc = ga_k_ingest(ctx->d_ring, slot->d_desc, n, ctx->d_arena, slot->d_res,
+                                 ctx->frames_cap ? slot->d_frames : nullptr, ctx->cfg.mode & GA_DO_ALL, ctx->cfg.vad_threshold, s);
+                if (rc) return rc;
+            } else {
+                GA_CUDA_TRY(cudaMemsetAsync(slot->d_res, 0, sizeof(ga_result) * n, s));
+            }
         } else {
             // fingerprint of the received bytes first (writes whole records), then the decimator
             // fills the statistics of the resampled samples into the same records
@@ -440,6 +473,15 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
             rc = ga_k_resample48(ctx->d_ring, slot->d_rdesc, n, ctx->d_hist, ctx->d_arena, slot->d_res,
                                  ctx->frames_cap ? slot->d_frames : nullptr, ctx->cfg.vad_threshold, s);
             if (rc) return rc;
+        }
+        if (utter) {
+            // the running digests make consecutive tickets dependent: chain them like the 48 kHz carry
+            GA_CUDA_TRY(cudaMemcpyAsync(slot->d_link, slot->h_link, sizeof(uint32_t) * 2 * ctx->cfg.max_batch_msgs, cudaMemcpyHostToDevice, s));
+            if (ctx->prev_kdone && !fmt48) GA_CUDA_TRY(cudaStreamWaitEvent(s, ctx->prev_kdone, 0));
+            rc = ga_k_sha256_chain(ctx->d_ring, slot->d_desc, slot->d_link + ctx->cfg.max_batch_msgs, slot->d_link, n_chains, ctx->d_sha, s);
+            if (rc) return rc;
+        }
+        if (fmt48 || utter) {
             GA_CUDA_TRY(cudaEventRecord(slot->kdone, s));
             ctx->prev_kdone = slot->kdone;
         }
@@ -552,6 +594,44 @@ extern "C" int ga_stream_reset(ga_ctx *ctx, uint32_t stream_id)
     if (!ctx || stream_id >= ctx->cfg.max_streams) { set_error("ga_stream_reset: bad argument"); return GA_ERR_ARG; }
     std::lock_guard<std::mutex> lk(ctx->mu);
     ctx->streams[stream_id] = StreamState();   // cleanupRelay, audio_service.go:916-923
+    if (ctx->d_sha) {
+        int rc = set_device(ctx);
+        if (rc) return rc;
+        rc = join_inflight(ctx, ctx->aux);
+        if (rc) return rc;
+        rc = ga_k_sha256_reset(ctx->d_sha + stream_id, 1, ctx->aux);
+        if (rc) return rc;
+        GA_CUDA_TRY(cudaStreamSynchronize(ctx->aux));
+    }
+    return GA_OK;
+}
+
+extern "C" int ga_utterance_digest(ga_ctx *ctx, uint32_t stream_id, uint8_t digest[32], uint64_t *total_bytes)
+{
+    if (!ctx || !digest || stream_id >= ctx->cfg.max_streams) { set_error("ga_utterance_digest: bad argument"); return GA_ERR_ARG; }
+    if (!ctx->d_sha) { set_error("ga_utterance_digest: context was not created with GA_DO_UTTERANCE"); return GA_ERR_STATE; }
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int rc = set_device(ctx);
+    if (rc) return rc;
+    rc = join_inflight(ctx, ctx->aux);
+    if (rc) return rc;
+    // 32-byte digest + 8-byte length land in the first 40 bytes of a scratch state record (the last one is spare)
+    struct Out { uint8_t d[32]; uint64_t len; } out;
+    uint8_t *d_out = nullptr;
+    GA_CUDA_TRY(cudaMalloc(reinterpret_cast<void **>(&d_out), 64 + sizeof(uint32_t)));
+    uint32_t sid = stream_id;
+    cudaError_t e = cudaMemcpyAsync(d_out + 64, &sid, sizeof sid, cudaMemcpyHostToDevice, ctx->aux);
+    if (e == cudaSuccess) {
+        rc = ga_k_sha256_final(ctx->d_sha, reinterpret_cast<uint32_t *>(d_out + 64), 1, d_out,
+                               reinterpret_cast<uint64_t *>(d_out + 32), ctx->aux);
+        if (rc == GA_OK) e = cudaMemcpyAsync(&out, d_out, 40, cudaMemcpyDeviceToHost, ctx->aux);
+        if (rc == GA_OK && e == cudaSuccess) e = cudaStreamSynchronize(ctx->aux);
+    }
+    cudaFree(d_out);
+    if (rc) return rc;
+    if (e != cudaSuccess) { set_error("ga_utterance_digest: %s", cudaGetErrorString(e)); return GA_ERR_CUDA; }
+    std::memcpy(digest, out.d, 32);
+    if (total_bytes) *total_bytes = out.len;
     return GA_OK;
 }
 
