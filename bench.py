@@ -56,6 +56,9 @@ def parse():
     ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS))
     ap.add_argument("--mode", default="fused", choices=["fused", "split"],
                     help="fused: one ingest launch; split: convert+features launch, then SHA-256 launch")
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
+                    help="N > 1: how guest scores reach their window's home shard — fused peer writes over "
+                         "NVLink inside the arbitration kernel (p2p) or score + NCCL all-gather + route + select")
     ap.add_argument("--ticks-per-submit", type=int, default=10)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -261,8 +264,25 @@ def main():
     n_route = len(plan.route_dst)
 
     ingest_ev, resample_ev = [], []
+    exchange = None
+    if world > 1 and args.exchange == "p2p":
+        from loqa_hub_b200 import p2p
+        region = p2p.Region(plan.n_guest_max, world)
+        handles = [None] * world
+        dist.all_gather_object(handles, bytes(region.handle))
+        bases = [region.ptr.value if r == rank else p2p.open_peer(handles[r]) for r in range(world)]
+        exchange = p2p.Exchange(plan, region, bases,
+                                dict(samples=dptr(samples), wake_off=dptr(d_wake_off), wake_n=dptr(d_wake_n),
+                                     status_in=dptr(d_status), seg=dptr(d_seg), scores=dptr(d_scores),
+                                     winner=dptr(d_winner), status_out=dptr(d_status_out)),
+                                lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev))
+        dist.barrier()
 
     def arbitration(samples_ptr):
+        if exchange is not None:      # one fused launch: score -> NVLink peer stores -> flags -> select
+            exchange.args.d_samples = samples_ptr
+            exchange.launch(sp)
+            return
         api.k_signal_strength(samples_ptr, dptr(d_wake_off), dptr(d_wake_n), dptr(d_status), n_members,
                               dptr(d_scores), 0, sp)
         if world > 1 and n_guest:
@@ -330,6 +350,18 @@ def main():
     expect = plan.seg_offsets[:-1].astype(np.int64)      # relay 0 has the highest gain in every group
     if not np.array_equal(win, expect):
         raise SystemExit("bench: arbitration winners are wrong on rank %d" % rank)
+    if exchange is not None and exchange.error_flag():
+        raise SystemExit("bench: cross-shard exchange timed out on rank %d" % rank)
+    if world > 1:
+        # the scores that crossed shards must be the guests' true scores: compare the routed slots
+        # with the same relays scored where they live (all-gathered once, outside the timed region)
+        mine = d_scores[n_slots:].clone()
+        allg = torch.zeros(max(world * n_guest, 1), dtype=torch.float64, device=dev)
+        if n_guest:
+            dist.all_gather_into_tensor(allg, mine)
+            got = d_scores[:n_slots].cpu().numpy()[plan.route_dst]
+            if not np.array_equal(got, allg.cpu().numpy()[plan.route_src]):
+                raise SystemExit("bench: routed cross-shard scores are wrong on rank %d" % rank)
 
     # ---- end to end through the host C ABI
     e2e = None
@@ -364,6 +396,7 @@ def main():
             "config": {"workload": args.workload + " per GPU: " + w["desc"] + "; 5 s utterances, saturated mode",
                        "streams_per_gpu": S, "msgs_per_step_per_gpu": n_msgs, "mode": args.mode,
                        "cross_shard_windows_per_gpu": plan.n_spanning_windows,
+                       "exchange": (args.exchange if world > 1 else "none"),
                        "l2": "inputs %.0f MB + outputs %.0f MB per step > 126 MB L2, no flush needed" % (
                            n_msgs * ms * 2 / 1e6, n_msgs * (ms * 4 + 64) / 1e6)},
             "roofline": {"bound": "hbm", "kernel": "ingest_kernel<%s>" % ("sha256 of 48 kHz bytes" if fmt48 else args.mode), "achieved": achieved,

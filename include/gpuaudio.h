@@ -231,6 +231,49 @@ int ga_k_arbitrate_noalloc(const float *d_samples, const uint64_t *d_wake_off, c
 int ga_k_route_scores(const double *d_gathered, const uint32_t *d_src_idx,
                       const uint32_t *d_dst_slot, uint32_t n, double *d_scores, void *stream);
 
+/* Fused cross-shard arbitration (SURVEY.md §8e end state): one launch per shard replaces
+ * ga_k_signal_strength + all-gather + ga_k_route_scores + ga_k_select.  No reference counterpart
+ * (the reference is one process).  Members [0, n_home_members) are the slots of this shard's home
+ * windows (remote ones with wake_n = 0), members [n_home_members, +n_guests) are local relays of
+ * windows homed elsewhere.  The kernel
+ *   1. scores all of them (exact reference order, as ga_k_arbitrate);
+ *   2. stores guest j's score to the 8-byte PEER address d_guest_dst[j] + (epoch & 1) *
+ *      inbox_parity_stride — the home shard's inbox, mapped over NVLink with ga_p2p_open;
+ *   3. its last block writes `epoch` to every address in d_notify (the home shards' flag words),
+ *      waits until every LOCAL flag word in d_wait is >= epoch (bounded by timeout_cycles; on
+ *      expiry d_error is set non-zero and the launch still completes), copies
+ *      d_inbox[parity][k] into d_scores[d_route_dst[k]] and runs the selection for all windows.
+ * epoch starts at 1 and grows by 1 per step on every shard; all shards must call once per step.
+ * d_counter / d_error: one zero-initialised uint32 each, owned by the caller. */
+typedef struct ga_p2p_args {
+    const float    *d_samples;
+    const uint64_t *d_wake_off;
+    const uint32_t *d_wake_n;
+    const uint8_t  *d_status_in;
+    const uint32_t *d_seg_offsets;
+    double         *d_scores;            /* [n_home_members + n_guests]                         */
+    uint32_t       *d_winner;
+    uint8_t        *d_status_out;        /* [n_home_members]                                    */
+    const uint64_t *d_guest_dst;         /* [n_guests] peer addresses (parity 0)                */
+    const uint64_t *d_notify;            /* [n_notify] peer flag addresses                      */
+    const uint64_t *d_wait;              /* [n_wait]   local flag addresses                     */
+    const double   *d_inbox;             /* local inbox, parity 0; parity 1 at +inbox_parity_stride */
+    const uint32_t *d_route_dst;         /* [n_in] member slot of inbox entry k                 */
+    uint32_t       *d_counter;
+    uint32_t       *d_error;
+    uint64_t        inbox_parity_stride; /* bytes                                               */
+    uint64_t        epoch;
+    long long       timeout_cycles;
+    uint32_t        n_windows, n_home_members, n_guests, n_notify, n_wait, n_in;
+} ga_p2p_args;
+int ga_k_arbitrate_p2p(const ga_p2p_args *args, void *stream);
+/* Device memory another process on the same node can map (cudaMalloc + CUDA IPC): zero-filled.
+ * ga_p2p_open maps a peer's allocation from its 64-byte handle. */
+int ga_p2p_alloc(uint64_t bytes, void **d_ptr, uint8_t handle[64]);
+int ga_p2p_open(const uint8_t handle[64], void **d_ptr);
+int ga_p2p_close(void *d_ptr);
+int ga_p2p_free(void *d_ptr);
+
 /* ===================================================================== context
  * Host-buffer layer: what internal/gpuaudio binds.  One context per GPU.        */
 

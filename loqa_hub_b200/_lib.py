@@ -40,6 +40,14 @@ FMT_MONO16K, FMT_STEREO48K = 0, 1
 assert DESC_DTYPE.itemsize == 32 and MSG_DTYPE.itemsize == 24 and RDESC_DTYPE.itemsize == 64
 
 
+class P2PArgs(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("d_samples", "d_wake_off", "d_wake_n", "d_status_in", "d_seg_offsets",
+                                          "d_scores", "d_winner", "d_status_out", "d_guest_dst", "d_notify",
+                                          "d_wait", "d_inbox", "d_route_dst", "d_counter", "d_error")] + \
+               [("inbox_parity_stride", C.c_uint64), ("epoch", C.c_uint64), ("timeout_cycles", C.c_longlong)] + \
+               [(n, C.c_uint32) for n in ("n_windows", "n_home_members", "n_guests", "n_notify", "n_wait", "n_in")]
+
+
 class Config(C.Structure):
     _fields_ = [("device", C.c_int32), ("max_streams", C.c_uint32), ("max_batch_msgs", C.c_uint32),
                 ("max_inflight", C.c_uint32), ("ring_bytes", C.c_uint64), ("arena_samples", C.c_uint64),
@@ -51,6 +59,11 @@ class Config(C.Structure):
 _vp, _u32, _u64, _i32, _sz = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int, C.c_size_t
 SYMBOLS = {
     "ga_k_ingest": (_i32, [_vp, _vp, _u32, _vp, _vp, _vp, _u32, C.c_double, _vp]),
+    "ga_k_arbitrate_p2p": (_i32, [C.POINTER(P2PArgs), _vp]),
+    "ga_p2p_alloc": (_i32, [_u64, C.POINTER(_vp), _vp]),
+    "ga_p2p_open": (_i32, [_vp, C.POINTER(_vp)]),
+    "ga_p2p_close": (_i32, [_vp]),
+    "ga_p2p_free": (_i32, [_vp]),
     "ga_k_sha256_chain": (_i32, [_vp, _vp, _vp, _vp, _u32, _vp, _vp]),
     "ga_k_sha256_final": (_i32, [_vp, _vp, _u32, _vp, _vp, _vp]),
     "ga_k_sha256_reset": (_i32, [_vp, _u32, _vp]),

@@ -13,6 +13,7 @@
 //                  member when nothing exceeded 0.0 (:542-547) — then Winner / Cancelled
 //                  for every member (:553-571).  Join order stands in for Go's random map
 //                  iteration order.
+#include <cstring>
 #include <mutex>
 
 #include "common.cuh"
@@ -26,10 +27,14 @@ constexpr int kArbRowStride = kArbSlice + 16;   // 33 x 16 B: conflict-free lane
 constexpr int kArbStageBytes = 32 * kArbRowStride;
 constexpr int kArbWarpBytes = kArbStages * kArbStageBytes + 128;
 
-__global__ void __launch_bounds__(kArbWarps * 32)
-score_kernel(const float *__restrict__ samples, const uint64_t *__restrict__ wake_off,
-             const uint32_t *__restrict__ wake_n, const uint8_t *__restrict__ status_in,
-             uint32_t n_members, double *__restrict__ scores, ga_result *__restrict__ stats)
+// Scores of members [0, n_members).  Members >= mirror_first additionally store their score to
+// mirror[m - mirror_first] + mirror_byte_off — an address in ANOTHER GPU's memory (NVLink peer
+// mapping) when a collision window spans shards; nullptr switches that off.
+__device__ __forceinline__ void
+score_tiles(const float *__restrict__ samples, const uint64_t *__restrict__ wake_off,
+            const uint32_t *__restrict__ wake_n, const uint8_t *__restrict__ status_in,
+            uint32_t n_members, double *__restrict__ scores, ga_result *__restrict__ stats,
+            uint32_t mirror_first, const uint64_t *__restrict__ mirror, uint64_t mirror_byte_off)
 {
     constexpr uint32_t FULL = 0xffffffffu;
     extern __shared__ __align__(128) uint8_t smem[];
@@ -104,16 +109,25 @@ score_kernel(const float *__restrict__ samples, const uint64_t *__restrict__ wak
                 ga_result *r = stats + m;
                 r->sumsq = sum; r->rms = rms; r->n_samples = n; r->nonzero = nz; r->peak = peak; r->flags = 0;
             }
+            if (mirror && m >= mirror_first)
+                *reinterpret_cast<volatile double *>(mirror[m - mirror_first] + mirror_byte_off) = rms;
         }
     }
 }
 
-__global__ void select_kernel(const double *__restrict__ scores, const uint8_t *__restrict__ status_in,
-                              const uint32_t *__restrict__ seg, uint32_t n_windows,
-                              uint32_t *__restrict__ winner, uint8_t *__restrict__ status_out)
+__global__ void __launch_bounds__(kArbWarps * 32)
+score_kernel(const float *__restrict__ samples, const uint64_t *__restrict__ wake_off,
+             const uint32_t *__restrict__ wake_n, const uint8_t *__restrict__ status_in,
+             uint32_t n_members, double *__restrict__ scores, ga_result *__restrict__ stats)
 {
-    const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
-    if (w >= n_windows) return;
+    score_tiles(samples, wake_off, wake_n, status_in, n_members, scores, stats, 0, nullptr, 0);
+}
+
+// One window: the reference's selection loop (:519-547) and status update (:553-571).
+__device__ __forceinline__ void select_window(const double *__restrict__ scores, const uint8_t *__restrict__ status_in,
+                                              const uint32_t *__restrict__ seg, uint32_t w,
+                                              uint32_t *__restrict__ winner, uint8_t *__restrict__ status_out)
+{
     const uint32_t a = seg[w], b = seg[w + 1];
     uint32_t win = 0xffffffffu;
     double best = 0.0;                                            // :519
@@ -126,6 +140,66 @@ __global__ void select_kernel(const double *__restrict__ scores, const uint8_t *
     winner[w] = win;
     for (uint32_t m = a; m < b; m++)                              // :553-571
         status_out[m] = (m == win) ? GA_RELAY_WINNER : GA_RELAY_CANCELLED;
+}
+
+// ---------------------------------------------------------------- fused cross-shard arbitration
+// score -> store guest scores into their home shard's inbox over NVLink -> raise a flag there ->
+// wait for the shards that owe us scores -> scatter the inbox into member slots -> select:
+// ONE launch per shard instead of score + all-gather + route + select.  Blocks score tiles; the
+// block that finishes last (atomic ticket) does the exchange and the selection.  The inbox is
+// double-buffered by step parity: a neighbour can be at most one step ahead of our selection,
+// because its next step cannot finish before it has seen our flag for that step.
+__device__ __forceinline__ void st_release_sys(uint64_t addr, uint64_t v)
+{
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(addr), "l"(v) : "memory");
+}
+__device__ __forceinline__ uint64_t ld_acquire_sys(uint64_t addr)
+{
+    uint64_t v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(addr) : "memory");
+    return v;
+}
+
+__global__ void __launch_bounds__(kArbWarps * 32)
+arbitrate_p2p_kernel(const ga_p2p_args a)
+{
+    __shared__ bool s_last;
+    const uint32_t n_all = a.n_home_members + a.n_guests;
+    const uint64_t parity_off = (a.epoch & 1ull) * a.inbox_parity_stride;
+    score_tiles(a.d_samples, a.d_wake_off, a.d_wake_n, a.d_status_in, n_all, a.d_scores, nullptr,
+                a.n_home_members, a.d_guest_dst, parity_off);
+    __threadfence_system();                     // my peer stores are visible before my block counts itself done
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = (atomicAdd(a.d_counter, 1u) == gridDim.x - 1);
+    __syncthreads();
+    if (!s_last) return;
+
+    // ---- last block: every score of this shard is written (locally and to the peers)
+    __threadfence_system();
+    if (threadIdx.x == 0) *a.d_counter = 0;     // ready for the next launch
+    for (uint32_t i = threadIdx.x; i < a.n_notify; i += blockDim.x) st_release_sys(a.d_notify[i], a.epoch);
+    for (uint32_t i = threadIdx.x; i < a.n_wait; i += blockDim.x) {
+        const long long t0 = clock64();
+        while (ld_acquire_sys(a.d_wait[i]) < a.epoch) {
+            if (clock64() - t0 > a.timeout_cycles) { atomicExch(a.d_error, 1u + i); break; }   // never hang the GPU
+            __nanosleep(200);
+        }
+    }
+    __syncthreads();
+    const volatile double *inbox = reinterpret_cast<const volatile double *>(
+        reinterpret_cast<const uint8_t *>(a.d_inbox) + parity_off);
+    for (uint32_t k = threadIdx.x; k < a.n_in; k += blockDim.x) a.d_scores[a.d_route_dst[k]] = inbox[k];
+    __syncthreads();
+    for (uint32_t w = threadIdx.x; w < a.n_windows; w += blockDim.x)
+        select_window(a.d_scores, a.d_status_in, a.d_seg_offsets, w, a.d_winner, a.d_status_out);
+}
+
+__global__ void select_kernel(const double *__restrict__ scores, const uint8_t *__restrict__ status_in,
+                              const uint32_t *__restrict__ seg, uint32_t n_windows,
+                              uint32_t *__restrict__ winner, uint8_t *__restrict__ status_out)
+{
+    const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w < n_windows) select_window(scores, status_in, seg, w, winner, status_out);
 }
 
 __global__ void route_kernel(const double *__restrict__ gathered, const uint32_t *__restrict__ src,
@@ -168,6 +242,79 @@ extern "C" int ga_k_route_scores(const double *d_gathered, const uint32_t *d_src
     if (!d_gathered || !d_src_idx || !d_dst_slot || !d_scores) { set_error("ga_k_route_scores: NULL argument"); return GA_ERR_ARG; }
     route_kernel<<<(n + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(d_gathered, d_src_idx, d_dst_slot, n, d_scores);
     GA_CHECK_LAUNCH("route_kernel");
+    return GA_OK;
+}
+
+extern "C" int ga_k_arbitrate_p2p(const ga_p2p_args *args, void *stream)
+{
+    using namespace ga;
+    if (!args) { set_error("ga_k_arbitrate_p2p: NULL argument"); return GA_ERR_ARG; }
+    const ga_p2p_args &a = *args;
+    if (a.n_windows == 0) return GA_OK;
+    const uint32_t n_all = a.n_home_members + a.n_guests;
+    if (!a.d_seg_offsets || !a.d_winner || !a.d_counter || !a.d_error ||
+        (n_all && (!a.d_samples || !a.d_wake_off || !a.d_wake_n || !a.d_status_in || !a.d_scores || !a.d_status_out)) ||
+        (a.n_guests && !a.d_guest_dst) || (a.n_notify && !a.d_notify) || (a.n_wait && !a.d_wait) ||
+        (a.n_in && (!a.d_inbox || !a.d_route_dst))) {
+        set_error("ga_k_arbitrate_p2p: NULL array in arguments");
+        return GA_ERR_ARG;
+    }
+    if (a.epoch == 0) { set_error("ga_k_arbitrate_p2p: epoch must start at 1 and increase by 1 per step"); return GA_ERR_ARG; }
+    static thread_local int configured_dev = -1;
+    int dev = 0;
+    GA_CUDA_TRY(cudaGetDevice(&dev));
+    constexpr int smem = kArbWarps * kArbWarpBytes;
+    if (configured_dev != dev) {
+        GA_CUDA_TRY(cudaFuncSetAttribute(arbitrate_p2p_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        configured_dev = dev;
+    }
+    const uint32_t n_tiles = (n_all + 31) / 32;
+    uint32_t grid = (n_tiles + kArbWarps - 1) / kArbWarps;
+    if (grid == 0) grid = 1;
+    arbitrate_p2p_kernel<<<grid, kArbWarps * 32, smem, static_cast<cudaStream_t>(stream)>>>(a);
+    GA_CHECK_LAUNCH("arbitrate_p2p_kernel");
+    return GA_OK;
+}
+
+// Peer-visible device memory for the inbox + flags (cudaMalloc + CUDA IPC handle).
+extern "C" int ga_p2p_alloc(uint64_t bytes, void **d_ptr, uint8_t handle[64])
+{
+    using namespace ga;
+    if (!d_ptr || !handle || bytes == 0) { set_error("ga_p2p_alloc: bad argument"); return GA_ERR_ARG; }
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    void *p = nullptr;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) { cudaGetLastError(); set_error("ga_p2p_alloc: %s", cudaGetErrorString(e)); return GA_ERR_NOMEM; }
+    GA_CUDA_TRY(cudaMemset(p, 0, bytes));
+    cudaIpcMemHandle_t h;
+    e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) { cudaFree(p); cudaGetLastError(); set_error("ga_p2p_alloc: cudaIpcGetMemHandle: %s", cudaGetErrorString(e)); return GA_ERR_CUDA; }
+    memcpy(handle, &h, 64);
+    *d_ptr = p;
+    return GA_OK;
+}
+
+extern "C" int ga_p2p_open(const uint8_t handle[64], void **d_ptr)
+{
+    using namespace ga;
+    if (!d_ptr || !handle) { set_error("ga_p2p_open: bad argument"); return GA_ERR_ARG; }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    GA_CUDA_TRY(cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return GA_OK;
+}
+
+extern "C" int ga_p2p_close(void *d_ptr)
+{
+    using namespace ga;
+    if (d_ptr) GA_CUDA_TRY(cudaIpcCloseMemHandle(d_ptr));
+    return GA_OK;
+}
+
+extern "C" int ga_p2p_free(void *d_ptr)
+{
+    using namespace ga;
+    if (d_ptr) GA_CUDA_TRY(cudaFree(d_ptr));
     return GA_OK;
 }
 
