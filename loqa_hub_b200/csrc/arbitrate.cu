@@ -20,9 +20,9 @@
 
 namespace ga {
 
-constexpr int kArbWarps = 2;
+constexpr int kArbWarps = 1;                    // 4,096 members are only 128 tiles: one warp per block spreads them over the SMs
 constexpr int kArbSlice = 512;                  // bytes of f32 per member per stage
-constexpr int kArbStages = 2;
+constexpr int kArbStages = 4;                   // deep enough that a lane's add chain never waits for the copy
 constexpr int kArbRowStride = kArbSlice + 16;   // 33 x 16 B: conflict-free lane-per-row LDS.128
 constexpr int kArbStageBytes = 32 * kArbRowStride;
 constexpr int kArbWarpBytes = kArbStages * kArbStageBytes + 128;
