@@ -362,6 +362,53 @@ int ga_arbitrate(ga_ctx *ctx, const uint32_t *seg_offsets, uint32_t n_windows,
                  const uint32_t *stream_ids, const uint8_t *status_in,
                  uint32_t *winner_idx, double *scores, uint8_t *status_out);
 
+/* Winner audio as a WAV file for the STT call (float32ToWAV, internal/llm/stt_client.go:365-398):
+ * 44-byte RIFF header (format 3 = IEEE float, mono, 32 bit) + WakeWordSignal ++ SpeechAudio copied
+ * device->host straight behind it.  out == NULL only reports the size in *n_bytes. */
+int ga_fetch_wav(ga_ctx *ctx, uint32_t stream_id, uint32_t sample_rate, uint8_t *out, size_t cap,
+                 size_t *n_bytes);
+
+/* ===================================================================== hub (window manager)
+ * Host-side mirror of the reference's AudioService for this path (internal/grpc/audio_service.go):
+ * relay registry, arbitration-window lifecycle, per-chunk routing.  It is the logic the Go code
+ * around this library keeps, provided in C++ so it can run and be tested
+ * without a Go toolchain, and generalised from the reference's single hub-wide window (:89) to one
+ * window per collision group.  Time is injected in microseconds.  Thread-safe (one mutex). */
+typedef struct ga_hub ga_hub;
+/* createAudioService :201-290; window_duration_us 0 = the reference's 300 ms (:243). */
+int  ga_hub_create(ga_ctx *ctx, uint32_t max_streams, uint64_t window_duration_us, ga_hub **out);
+void ga_hub_destroy(ga_hub *hub);
+/* A relay opened its stream (StreamAudio :926); assigns it a stream slot of the context. */
+int  ga_hub_connect(ga_hub *hub, const char *relay_id, uint32_t group, uint32_t *slot);
+/* startArbitrationWindow :408-446 / joinArbitrationWindow :449-491 (joined = 0: no window, window
+ * already arbitrated, or elapsed > duration). */
+int  ga_hub_start_window(ga_hub *hub, const char *relay_id, uint64_t now_us, uint64_t *window_id);
+int  ga_hub_join_window(ga_hub *hub, const char *relay_id, uint64_t now_us, int *joined);
+/* The body of the StreamAudio loop for one AudioChunk (:939-1041): wake-word chunks start or join
+ * the group's window and extend WakeWordSignal, other chunks extend SpeechAudio of relays that are
+ * in activeStreams; the bytes go into the pinned ring and are queued for the next flush.
+ * *keep_stream = 0 where the reference handler returns (late relay :990-995, cancelled at
+ * end of speech :1018-1021). */
+int  ga_hub_on_chunk(ga_hub *hub, const char *relay_id, const uint8_t *audio, uint32_t nbytes,
+                     int is_wake_word, int is_end_of_speech, uint64_t now_us, int *keep_stream);
+/* Batch tick: one ga_submit + wait for everything queued since the last flush. */
+int  ga_hub_flush(ga_hub *hub, uint32_t *n_msgs);
+/* performArbitration :505-587 for one window (idempotent, :508-511) … */
+int  ga_hub_perform_arbitration(ga_hub *hub, uint64_t window_id);
+/* … and runArbitrationTimer :494-502 for all groups: every active window whose duration has
+ * elapsed at now_us is arbitrated in ONE ga_arbitrate call. */
+int  ga_hub_poll(ga_hub *hub, uint64_t now_us, uint32_t *n_closed);
+int  ga_hub_window_info(ga_hub *hub, uint64_t window_id, int *is_active, char *winner_id,
+                        size_t winner_cap, uint32_t *n_relays);
+int  ga_hub_active_window(ga_hub *hub, uint32_t group, uint64_t *window_id);   /* 0 = nil */
+int  ga_hub_relay_info(ga_hub *hub, const char *relay_id, int *status, double *signal_strength,
+                       int *cancel_closed, uint32_t *slot);
+int  ga_hub_is_relay_active(ga_hub *hub, const char *relay_id);                /* isRelayActive :880-913 */
+int  ga_hub_set_relay_status(ga_hub *hub, const char *relay_id, int status);   /* as.activeStreams[id].Status = … */
+int  ga_hub_complete_request(ga_hub *hub, const char *relay_id);               /* collision_detection_test.go:361-369 */
+int  ga_hub_cleanup_relay(ga_hub *hub, const char *relay_id);                  /* cleanupRelay :916-923 */
+int  ga_hub_active_streams(ga_hub *hub, uint32_t *n);                          /* len(as.activeStreams) */
+
 /* --------------------------------------------------------------- one-shot mirrors
  * Same argument meaning and degenerate-input behaviour as the Go functions; used by
  * the parity tests and by callers that have a single buffer. */

@@ -87,6 +87,24 @@ SYMBOLS = {
     "ga_stream_reset": (_i32, [_vp, _u32]),
     "ga_device_arena": (_i32, [_vp, C.POINTER(_vp)]),
     "ga_arbitrate": (_i32, [_vp, _vp, _u32, _vp, _vp, _vp, _vp, _vp]),
+    "ga_fetch_wav": (_i32, [_vp, _u32, _u32, _vp, _sz, C.POINTER(_sz)]),
+    "ga_hub_create": (_i32, [_vp, _u32, _u64, C.POINTER(_vp)]),
+    "ga_hub_destroy": (None, [_vp]),
+    "ga_hub_connect": (_i32, [_vp, C.c_char_p, _u32, C.POINTER(_u32)]),
+    "ga_hub_start_window": (_i32, [_vp, C.c_char_p, _u64, C.POINTER(_u64)]),
+    "ga_hub_join_window": (_i32, [_vp, C.c_char_p, _u64, C.POINTER(_i32)]),
+    "ga_hub_on_chunk": (_i32, [_vp, C.c_char_p, _vp, _u32, _i32, _i32, _u64, C.POINTER(_i32)]),
+    "ga_hub_flush": (_i32, [_vp, C.POINTER(_u32)]),
+    "ga_hub_perform_arbitration": (_i32, [_vp, _u64]),
+    "ga_hub_poll": (_i32, [_vp, _u64, C.POINTER(_u32)]),
+    "ga_hub_window_info": (_i32, [_vp, _u64, C.POINTER(_i32), C.c_char_p, _sz, C.POINTER(_u32)]),
+    "ga_hub_active_window": (_i32, [_vp, _u32, C.POINTER(_u64)]),
+    "ga_hub_relay_info": (_i32, [_vp, C.c_char_p, C.POINTER(_i32), C.POINTER(C.c_double), C.POINTER(_i32), C.POINTER(_u32)]),
+    "ga_hub_is_relay_active": (_i32, [_vp, C.c_char_p]),
+    "ga_hub_set_relay_status": (_i32, [_vp, C.c_char_p, _i32]),
+    "ga_hub_complete_request": (_i32, [_vp, C.c_char_p]),
+    "ga_hub_cleanup_relay": (_i32, [_vp, C.c_char_p]),
+    "ga_hub_active_streams": (_i32, [_vp, C.POINTER(_u32)]),
     "ga_bytes_to_float32": (_i32, [_vp, _vp, _sz, _vp, C.POINTER(_sz), _vp]),
     "ga_signal_strength": (_i32, [_vp, _vp, _sz, C.POINTER(C.c_double), _vp]),
     "ga_sha256": (_i32, [_vp, _vp, _sz, _vp]),
