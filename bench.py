@@ -59,6 +59,9 @@ def parse():
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                     help="N > 1: how guest scores reach their window's home shard — fused peer writes over "
                          "NVLink inside the arbitration kernel (p2p) or score + NCCL all-gather + route + select")
+    ap.add_argument("--staging", default="tmap", choices=["tmap", "bulk"],
+                    help="how message bytes reach shared memory: one 2-D TMA tensor copy per 32 messages "
+                         "(uniform batches) or one bulk copy per message")
     ap.add_argument("--ticks-per-submit", type=int, default=10)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -292,17 +295,22 @@ def main():
         api.k_select(dptr(d_scores), dptr(d_status), dptr(d_seg), plan.n_windows, dptr(d_winner),
                      dptr(d_status_out), sp)
 
+    def ingest(mode, smp):
+        if args.staging == "tmap":
+            api.k_ingest_uniform(dptr(pcm), dptr(d_desc), n_msgs, 0, msg_bytes, msg_bytes, smp, dptr(results), 0, mode, 0.01, sp)
+        else:
+            api.k_ingest(dptr(pcm), dptr(d_desc), n_msgs, smp, dptr(results), 0, mode, 0.01, sp)
+
     def step(timed):
         if timed:
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record(stream)
         if fmt48:       # fingerprint of the received bytes (timed as the dominant kernel), then the decimator
-            api.k_ingest(dptr(pcm), dptr(d_desc), n_msgs, 0, dptr(results), 0, L.DO_SHA256, 0.01, sp)
+            ingest(L.DO_SHA256, 0)
         elif args.mode == "fused":
-            api.k_ingest(dptr(pcm), dptr(d_desc), n_msgs, dptr(samples), dptr(results), 0, L.DO_ALL, 0.01, sp)
+            ingest(L.DO_ALL, dptr(samples))
         else:
-            api.k_ingest(dptr(pcm), dptr(d_desc), n_msgs, dptr(samples), dptr(results), 0,
-                         L.DO_CONVERT | L.DO_FEATURES, 0.01, sp)
+            ingest(L.DO_CONVERT | L.DO_FEATURES, dptr(samples))
         if timed:
             b.record(stream)
             ingest_ev.append((a, b))
@@ -315,7 +323,7 @@ def main():
                 d.record(stream)
                 resample_ev.append((c, d))
         elif args.mode == "split":
-            api.k_ingest(dptr(pcm), dptr(d_desc), n_msgs, 0, dptr(results), 0, L.DO_SHA256, 0.01, sp)
+            ingest(L.DO_SHA256, 0)
         arbitration(dptr(samples))
 
     def sync_all():
@@ -395,6 +403,7 @@ def main():
             "data": "synthetic",
             "config": {"workload": args.workload + " per GPU: " + w["desc"] + "; 5 s utterances, saturated mode",
                        "streams_per_gpu": S, "msgs_per_step_per_gpu": n_msgs, "mode": args.mode,
+                       "staging": args.staging,
                        "cross_shard_windows_per_gpu": plan.n_spanning_windows,
                        "exchange": (args.exchange if world > 1 else "none"),
                        "l2": "inputs %.0f MB + outputs %.0f MB per step > 126 MB L2, no flush needed" % (
@@ -440,7 +449,8 @@ def run_e2e(args, w, plan, pcm, arbitration, d_winner, world, rank, local_rank, 
     ring_bytes = sub_bytes * n_sub
     ctx = api.Context(device=local_rank, max_streams=S, max_batch_msgs=sub_msgs, max_inflight=4,
                       ring_bytes=ring_bytes, arena_samples=M * ms, wake_samples_max=wake * ms,
-                      mode=L.DO_ALL, want_frames=False)
+                      mode=L.DO_ALL, want_frames=False,
+                      staging=L.STAGING_AUTO if args.staging == "tmap" else L.STAGING_BULK)
     import ctypes as C
     arena_ptr = C.c_void_p()
     L.check(L.load().ga_device_arena(ctx._h, C.byref(arena_ptr)))

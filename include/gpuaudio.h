@@ -116,6 +116,17 @@ int ga_k_ingest(const void *d_pcm, const ga_desc *d_desc, uint32_t n_msgs,
                 float *d_samples, ga_result *d_results, ga_frame *d_frames,
                 uint32_t mode, double vad_threshold, void *stream);
 
+/* ga_k_ingest for a UNIFORM batch: message i is the msg_bytes bytes at
+ * d_pcm + first_in_off + i * msg_stride (what a batch tick of equal-sized chunks copied into the
+ * ring in order looks like); desc[i].in_off / nbytes are ignored, everything else is as in
+ * ga_k_ingest and the results are identical.  The slab is described by a 2-D TMA tensor map, so one
+ * hardware copy per 32-message slice replaces 32 per-message bulk copies.  first_in_off and
+ * msg_stride must be multiples of 16. */
+int ga_k_ingest_uniform(const void *d_pcm, const ga_desc *d_desc, uint32_t n_msgs,
+                        uint64_t first_in_off, uint32_t msg_bytes, uint64_t msg_stride,
+                        float *d_samples, ga_result *d_results, ga_frame *d_frames,
+                        uint32_t mode, double vad_threshold, void *stream);
+
 /* Segmented per-collision-window arbitration — replaces the scoring + selection of
  * performArbitration, audio_service.go:517-571, for n_windows windows at once.
  * Window w owns members [seg_offsets[w], seg_offsets[w+1]) in join order.  Member m's
@@ -293,8 +304,12 @@ typedef struct ga_config {
     uint32_t want_frames;       /* != 0: per-frame records are produced and returned   */
     double   vad_threshold;     /* VAD flag = rms > threshold (default 0.01)           */
     uint32_t input_format;      /* GA_FMT_*: what every message of this context holds  */
-    uint32_t reserved;
+    uint32_t staging;           /* GA_STAGING_*: how message bytes reach shared memory  */
 } ga_config;
+#define GA_STAGING_AUTO  0u     /* uniform batches (equal chunk sizes, back to back in the ring) use
+                                   one 2-D TMA tensor copy per 32 messages, others one bulk copy
+                                   per message                                               */
+#define GA_STAGING_BULK  1u     /* always one bulk copy per message                         */
 #define GA_FMT_MONO16K   0u     /* 16 kHz mono int16 — what the reference assumes (:609) */
 #define GA_FMT_STEREO48K 1u     /* 48 kHz interleaved stereo int16, resampled to 16 kHz mono;
                                    chunks of at most GA_RS_MAX_MSG_BYTES; a chunk that follows

@@ -37,6 +37,7 @@ RDESC_DTYPE = np.dtype([("in_off", "<u8"), ("out_off", "<u8"), ("hist_off", "<u8
 HIST_ZERO, HIST_SLAB, HIST_STATE = 0, 1, 2
 RS_SAVE_HIST = 0x10000
 FMT_MONO16K, FMT_STEREO48K = 0, 1
+STAGING_AUTO, STAGING_BULK = 0, 1
 assert DESC_DTYPE.itemsize == 32 and MSG_DTYPE.itemsize == 24 and RDESC_DTYPE.itemsize == 64
 
 
@@ -52,7 +53,7 @@ class Config(C.Structure):
     _fields_ = [("device", C.c_int32), ("max_streams", C.c_uint32), ("max_batch_msgs", C.c_uint32),
                 ("max_inflight", C.c_uint32), ("ring_bytes", C.c_uint64), ("arena_samples", C.c_uint64),
                 ("wake_samples_max", C.c_uint64), ("mode", C.c_uint32), ("want_frames", C.c_uint32),
-                ("vad_threshold", C.c_double), ("input_format", C.c_uint32), ("reserved", C.c_uint32)]
+                ("vad_threshold", C.c_double), ("input_format", C.c_uint32), ("staging", C.c_uint32)]
 
 
 # every symbol include/gpuaudio.h declares: name -> (restype, argtypes)
@@ -69,6 +70,7 @@ SYMBOLS = {
     "ga_k_sha256_reset": (_i32, [_vp, _u32, _vp]),
     "ga_utterance_digest": (_i32, [_vp, _u32, _vp, C.POINTER(_u64)]),
     "ga_k_resample48": (_i32, [_vp, _vp, _u32, _vp, _vp, _vp, _vp, C.c_double, _vp]),
+    "ga_k_ingest_uniform": (_i32, [_vp, _vp, _u32, _u64, _u32, _u64, _vp, _vp, _vp, _u32, C.c_double, _vp]),
     "ga_k_arbitrate": (_i32, [_vp, _vp, _vp, _vp, _vp, _u32, _u32, _vp, _vp, _vp, _vp]),
     "ga_k_arbitrate_noalloc": (_i32, [_vp, _vp, _vp, _vp, _vp, _u32, _u32, _vp, _vp, _vp]),
     "ga_k_signal_strength": (_i32, [_vp, _vp, _vp, _vp, _u32, _vp, _vp, _vp]),

@@ -56,6 +56,13 @@ def k_resample48(d_pcm, d_rdesc, n_msgs, d_hist_state, d_samples, d_results, d_f
                                  d_frames or None, vad_threshold, stream or None))
 
 
+def k_ingest_uniform(d_pcm, d_desc, n_msgs, first_in_off, msg_bytes, msg_stride, d_samples, d_results,
+                     d_frames=0, mode=L.DO_ALL, vad_threshold=0.01, stream=0):
+    check(load().ga_k_ingest_uniform(d_pcm, d_desc, n_msgs, first_in_off, msg_bytes, msg_stride,
+                                     d_samples or None, d_results, d_frames or None, mode, vad_threshold,
+                                     stream or None))
+
+
 def k_arbitrate(d_samples, d_wake_off, d_wake_n, d_status_in, d_seg, n_windows, n_members,
                 d_scores, d_winner, d_status_out, stream=0):
     check(load().ga_k_arbitrate(d_samples, d_wake_off, d_wake_n, d_status_in, d_seg, n_windows,
@@ -128,10 +135,11 @@ class Context:
 
     def __init__(self, device=0, max_streams=1024, max_batch_msgs=65536, max_inflight=4,
                  ring_bytes=64 << 20, arena_samples=80_000, wake_samples_max=8_000,
-                 mode=L.DO_ALL, want_frames=False, vad_threshold=0.01, input_format=L.FMT_MONO16K):
+                 mode=L.DO_ALL, want_frames=False, vad_threshold=0.01, input_format=L.FMT_MONO16K,
+                 staging=L.STAGING_AUTO):
         self.cfg = Config(device, max_streams, max_batch_msgs, max_inflight, ring_bytes,
                           arena_samples, wake_samples_max, mode, 1 if want_frames else 0,
-                          vad_threshold, input_format, 0)
+                          vad_threshold, input_format, staging)
         self._h = C.c_void_p()
         check(load().ga_init(C.byref(self.cfg), C.byref(self._h)))
         self._pending = {}

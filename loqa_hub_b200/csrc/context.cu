@@ -320,6 +320,10 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
     uint32_t n_chains = 0;
     ga_rdesc *rdescs = slot->h_rdesc;
     const uint64_t stamp = ctx->next_ticket;      // marks streams already seen in THIS batch
+    // equal-sized chunks copied into the ring back to back (a batch tick) can be staged by one
+    // 2-D TMA copy per 32 messages instead of one bulk copy per message
+    bool uniform = n > 0;
+    uint64_t phys0 = 0, ustride = 0;
     for (; i < n; i++) {
         const ga_msg &m = msgs[i];
         const uint64_t need = (static_cast<uint64_t>(m.nbytes) + 15u) & ~15ull;
@@ -330,6 +334,8 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
             err = GA_ERR_ARG;
             break;
         }
+        if (i == 0) { phys0 = phys; ustride = need; }
+        else if (uniform) uniform = (m.nbytes == msgs[0].nbytes) && (phys == phys0 + i * ustride);
         StreamState &st = streams[m.stream_id];
         if (m.flags & GA_MSG_FIRST) { resets.push_back({st}); st = StreamState(); }
         uint64_t ns = m.nbytes >> 1;
@@ -451,8 +457,12 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
         GA_CUDA_TRY(cudaMemcpyAsync(slot->d_desc, slot->h_desc, sizeof(ga_desc) * n, cudaMemcpyHostToDevice, s));
         if (!fmt48) {
             if (ctx->cfg.mode & GA_DO_ALL) {
-                rc = ga_k_ingest(ctx->d_ring, slot->d_desc, n, ctx->d_arena, slot->d_res,
-                                 ctx->frames_cap ? slot->d_frames : nullptr, ctx->cfg.mode & GA_DO_ALL, ctx->cfg.vad_threshold, s);
+                if (uniform && msgs[0].nbytes && ctx->cfg.staging != GA_STAGING_BULK)
+                    rc = ga_k_ingest_uniform(ctx->d_ring, slot->d_desc, n, phys0, msgs[0].nbytes, ustride, ctx->d_arena, slot->d_res,
+                                             ctx->frames_cap ? slot->d_frames : nullptr, ctx->cfg.mode & GA_DO_ALL, ctx->cfg.vad_threshold, s);
+                else
+                    rc = ga_k_ingest(ctx->d_ring, slot->d_desc, n, ctx->d_arena, slot->d_res,
+                                     ctx->frames_cap ? slot->d_frames : nullptr, ctx->cfg.mode & GA_DO_ALL, ctx->cfg.vad_threshold, s);
                 if (rc) return rc;
             } else {
                 GA_CUDA_TRY(cudaMemsetAsync(slot->d_res, 0, sizeof(ga_result) * n, s));

@@ -24,8 +24,18 @@
 //             without SHA-256 (0.43 ms vs 0.91 ms).
 // A third variant staged the samples in shared memory and used TMA bulk stores; with 128-256 B
 // per store and the proxy fence it was slower than both (tuning log).
+// Staging has two forms (bit 2 of COOP).  Generic batches (ragged lengths, arbitrary offsets):
+// one 1-D bulk copy per lane per slice — the instruction takes uniform registers, so the
+// compiler serialises the 32 lanes (a 32-iteration R2UR/ELECT loop, ~17 % of the instructions of
+// the HBM-bound instantiation).  Uniform batches (equal lengths at a constant stride, e.g. one
+// 20 ms chunk per stream per tick laid out in arrival order): the slab is described by a 2-D TMA
+// tensor map [message][byte] and ONE cp.async.bulk.tensor.2d per slice brings in the 32 x 128 B
+// box, 128-byte swizzled so that lane-per-row 16-byte reads hit eight different bank groups.
 // No tensor cores: nothing here is a contraction.
+#include <cuda.h>
+
 #include <cstdlib>
+#include <cstring>
 
 #include "common.cuh"
 #include "sha256.cuh"
@@ -34,12 +44,15 @@ namespace ga {
 
 constexpr int kWarpsPerBlock = 4;
 
-template <int CH, int STAGES>
+template <int CH, int STAGES, bool TMAP = false>
 struct TileSmem {
-    static constexpr int kRowStride = CH + 16;          // (CH/16 + 1) is odd -> conflict-free LDS.128
+    // generic: rows padded by 16 B ((CH/16 + 1) odd -> conflict-free LDS.128);
+    // tensor-map: dense 128-byte rows, 128B-swizzled by the TMA unit, stages 1024-byte aligned
+    static constexpr int kRowStride = TMAP ? CH : CH + 16;
     static constexpr int kStageBytes = 32 * kRowStride;
     static constexpr int kBarBase = STAGES * kStageBytes;
-    static constexpr int kWarpBytes = kBarBase + 128;   // + barriers (padded)
+    static constexpr int kWarpBytes = kBarBase + (TMAP ? 1024 : 128);   // + barriers (padded)
+    static_assert(!TMAP || CH == 128, "the swizzled layout is written for 128-byte slices");
     static_assert(CH % 64 == 0, "slices must hold whole SHA-256 blocks");
     static_assert(((CH / 16) + 1) % 2 == 1, "row stride must be an odd number of 16-byte units");
 };
@@ -53,7 +66,27 @@ struct IngestParams {
     double vad;
     uint32_t n_msgs;
     uint32_t n_tiles;
+    uint32_t msg_bytes;   // uniform batches only
 };
+
+// One 2-D box [32 rows x 128 bytes] of the slab -> shared memory (SASS UTMALDG).
+__device__ __forceinline__ void tma_load_box(void *smem_dst, const CUtensorMap *tmap, uint32_t col, uint32_t row,
+                                             uint64_t *bar)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::
+            "r"(smem_u32(smem_dst)),
+        "l"(tmap), "r"(col), "r"(row), "r"(smem_u32(bar))
+        : "memory");
+}
+
+// Address of byte `off` (16-byte granular swizzle) of row r in a stage.
+template <bool TMAP, int ROW_STRIDE>
+__device__ __forceinline__ const uint8_t *row_addr(const uint8_t *sbase, uint32_t r, uint32_t off)
+{
+    if (TMAP) return sbase + r * 128u + ((((off >> 4) ^ (r & 7u)) << 4) | (off & 15u));
+    return sbase + r * ROW_STRIDE + off;
+}
 
 // Two int16 samples -> two exact floats without the conversion (XU) pipe: bias each half
 // by 0x8000, splice it under the exponent of 2^23 and subtract 2^23 + 32768.
@@ -95,16 +128,17 @@ struct Span {
 
 template <int CH, int STAGES, uint32_t MODE, int COOP>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
-ingest_kernel(const IngestParams p)
+ingest_kernel(const IngestParams p, const __grid_constant__ CUtensorMap tmap)
 {
-    using L = TileSmem<CH, STAGES>;
-    constexpr bool kCoop = (MODE & GA_DO_CONVERT) != 0 && COOP == 1;      // cooperative store pass
-    constexpr bool kLaneStore = (MODE & GA_DO_CONVERT) != 0 && COOP == 0; // lane stores its own samples
+    constexpr bool kTmap = (COOP & 4) != 0;                                       // 2-D TMA staging (uniform batches)
+    using L = TileSmem<CH, STAGES, kTmap>;
+    constexpr bool kCoop = (MODE & GA_DO_CONVERT) != 0 && (COOP & 1) == 1;      // cooperative store pass
+    constexpr bool kLaneStore = (MODE & GA_DO_CONVERT) != 0 && (COOP & 1) == 0; // lane stores its own samples
     constexpr bool kFeat = (MODE & GA_DO_FEATURES) != 0;
     constexpr bool kSha = (MODE & GA_DO_SHA256) != 0;
     constexpr uint32_t FULL = 0xffffffffu;
 
-    extern __shared__ __align__(128) uint8_t smem[];
+    extern __shared__ __align__(1024) uint8_t smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint8_t *wbase = smem + warp * L::kWarpBytes;
     uint64_t *bars = reinterpret_cast<uint64_t *>(wbase + L::kBarBase);
@@ -124,7 +158,9 @@ ingest_kernel(const IngestParams p)
     uint64_t p_in = 0;
     auto p_load = [&]() {
         p_nb = 0; p_in = 0; p_nch = 0;
-        if (p_tile < p.n_tiles) {
+        if (kTmap) {
+            p_nch = p.msg_bytes ? (p.msg_bytes - 1) / CH + 1 : 1;
+        } else if (p_tile < p.n_tiles) {
             uint32_t i = p_tile * 32 + lane;
             uint32_t nch = 0;
             if (i < p.n_msgs) {
@@ -138,14 +174,22 @@ ingest_kernel(const IngestParams p)
     auto produce = [&](int stage) {
         if (p_tile >= p.n_tiles) return;                       // warp-uniform
         const uint32_t lo = p_chunk * CH;
-        uint32_t bytes = p_nb > lo ? min(p_nb - lo, static_cast<uint32_t>(CH)) : 0u;
-        bytes = (bytes + 15u) & ~15u;
-        const uint32_t total = __reduce_add_sync(FULL, bytes);
-        if (lane == 0) mbar_arrive_expect_tx(&bars[stage], total);
-        __syncwarp();
-        if (bytes)
-            bulk_g2s(wbase + stage * L::kStageBytes + lane * L::kRowStride, p.pcm + p_in + lo,
-                     bytes, &bars[stage]);
+        if (kTmap) {
+            // one box for the whole warp tile; rows / columns outside the tensor arrive as zeros
+            if (lane == 0) {
+                mbar_arrive_expect_tx(&bars[stage], L::kStageBytes);
+                tma_load_box(wbase + stage * L::kStageBytes, &tmap, lo, p_tile * 32u, &bars[stage]);
+            }
+        } else {
+            uint32_t bytes = p_nb > lo ? min(p_nb - lo, static_cast<uint32_t>(CH)) : 0u;
+            bytes = (bytes + 15u) & ~15u;
+            const uint32_t total = __reduce_add_sync(FULL, bytes);
+            if (lane == 0) mbar_arrive_expect_tx(&bars[stage], total);
+            __syncwarp();
+            if (bytes)
+                bulk_g2s(wbase + stage * L::kStageBytes + lane * L::kRowStride, p.pcm + p_in + lo,
+                         bytes, &bars[stage]);
+        }
         if (++p_chunk == p_nch) {
             p_tile += nw;
             p_chunk = 0;
@@ -166,7 +210,7 @@ ingest_kernel(const IngestParams p)
         uint64_t out_off = 0;
         if (valid) {
             const ga_desc d = p.desc[mi];
-            nb = d.nbytes; flags = d.flags; frame_off = d.frame_off; out_off = d.out_off;
+            nb = kTmap ? p.msg_bytes : d.nbytes; flags = d.flags; frame_off = d.frame_off; out_off = d.out_off;
         }
         const uint32_t my_nch = valid ? (nb ? (nb - 1) / CH + 1 : 1) : 0;
         const uint32_t c_nch = __reduce_max_sync(FULL, my_nch);
@@ -223,7 +267,7 @@ ingest_kernel(const IngestParams p)
                     const uint64_t r_out = __shfl_sync(FULL, out_off, row);
                     const uint32_t byte0 = lo + col * 8;
                     if (byte0 < r_even) {
-                        const uint2 raw = *reinterpret_cast<const uint2 *>(sbase + row * L::kRowStride + col * 8);
+                        const uint2 raw = *reinterpret_cast<const uint2 *>(row_addr<kTmap, L::kRowStride>(sbase, row, col * 8));
                         float v0, v1, v2, v3;
                         unpack2(raw.x, v0, v1);
                         unpack2(raw.y, v2, v3);
@@ -247,7 +291,6 @@ ingest_kernel(const IngestParams p)
             // contributes, including the padding block(s) when the message ends here, so the
             // unrolled compression exists once in the instruction stream.
             if ((kFeat || kSha || kLaneStore) && c < my_nch) {
-                const uint8_t *rowp = sbase + lane * L::kRowStride;
                 const uint32_t span = min(nb, lo + CH) - lo;
                 const uint32_t nfull = span >> 6;
                 const uint32_t rem = span & 63u;
@@ -257,10 +300,9 @@ ingest_kernel(const IngestParams p)
                     const uint32_t vb = b < nfull ? 64u : (b == nfull ? rem : 0u);   // data bytes in this block
                     uint32_t w[16];
                     if (vb) {
-                        const uint4 *q = reinterpret_cast<const uint4 *>(rowp + b * 64);
 #pragma unroll
                         for (int j = 0; j < 4; j++) {
-                            const uint4 t = q[j];
+                            const uint4 t = *reinterpret_cast<const uint4 *>(row_addr<kTmap, L::kRowStride>(sbase, lane, b * 64 + 16 * j));
                             w[4 * j] = t.x; w[4 * j + 1] = t.y; w[4 * j + 2] = t.z; w[4 * j + 3] = t.w;
                         }
                     } else {
@@ -295,9 +337,8 @@ ingest_kernel(const IngestParams p)
                         } else if (vb >= 2) {
                             // tail of the message: fewer than 32 samples, rolled loop from shared memory
                             const uint32_t ns = vb >> 1;           // an odd trailing byte is not a sample
-                            const uint16_t *hp = reinterpret_cast<const uint16_t *>(rowp + b * 64);
                             for (uint32_t k = 0; k < ns; k++) {
-                                const uint32_t h = hp[k];
+                                const uint32_t h = *reinterpret_cast<const uint16_t *>(row_addr<kTmap, L::kRowStride>(sbase, lane, b * 64 + 2 * k));
                                 float v0, v1;
                                 unpack2(h, v0, v1);
                                 const float x0 = pcm_to_f32(v0);
@@ -369,9 +410,9 @@ ingest_kernel(const IngestParams p)
 
 // ---------------------------------------------------------------- host launcher
 template <int CH, int STAGES, uint32_t MODE, int COOP>
-static int launch_ingest(const IngestParams &p, cudaStream_t st)
+static int launch_ingest(const IngestParams &p, const CUtensorMap &tmap, cudaStream_t st)
 {
-    using L = TileSmem<CH, STAGES>;
+    using L = TileSmem<CH, STAGES, (COOP & 4) != 0>;
     constexpr int smem = kWarpsPerBlock * L::kWarpBytes;
     auto kern = ingest_kernel<CH, STAGES, MODE, COOP>;
     static thread_local int configured_dev = -1;
@@ -392,9 +433,41 @@ static int launch_ingest(const IngestParams &p, cudaStream_t st)
     uint32_t grid = static_cast<uint32_t>(sms * blocks_per_sm);
     if (grid > want) grid = want;
     if (grid == 0) return GA_OK;
-    kern<<<grid, kWarpsPerBlock * 32, smem, st>>>(p);
+    kern<<<grid, kWarpsPerBlock * 32, smem, st>>>(p, tmap);
     GA_CHECK_LAUNCH("ingest_kernel");
     return GA_OK;
+}
+
+static int check_ingest_args(const char *who, const void *d_pcm, const ga_desc *d_desc, float *d_samples,
+                             ga_result *d_results, uint32_t &mode)
+{
+    if (!d_pcm || !d_desc || !d_results) { set_error("%s: NULL pcm/desc/results", who); return GA_ERR_ARG; }
+    mode &= GA_DO_ALL;
+    if (mode == 0) { set_error("%s: empty mode", who); return GA_ERR_ARG; }
+    if ((mode & GA_DO_CONVERT) && !d_samples) { set_error("%s: GA_DO_CONVERT needs d_samples", who); return GA_ERR_ARG; }
+    if ((reinterpret_cast<uintptr_t>(d_pcm) & 15u) || (reinterpret_cast<uintptr_t>(d_samples) & 15u) ||
+        (reinterpret_cast<uintptr_t>(d_results) & 15u) || (reinterpret_cast<uintptr_t>(d_desc) & 15u)) {
+        set_error("%s: device pointers must be 16-byte aligned", who);
+        return GA_ERR_ARG;
+    }
+    return GA_OK;
+}
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link against libcuda)
+typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                    const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static encode_tiled_fn get_encode_tiled()
+{
+    static encode_tiled_fn fn = [] {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return reinterpret_cast<encode_tiled_fn>(p);
+    }();
+    return fn;
 }
 
 }  // namespace ga
@@ -405,15 +478,8 @@ extern "C" int ga_k_ingest(const void *d_pcm, const ga_desc *d_desc, uint32_t n_
 {
     using namespace ga;
     if (n_msgs == 0) return GA_OK;
-    if (!d_pcm || !d_desc || !d_results) { set_error("ga_k_ingest: NULL pcm/desc/results"); return GA_ERR_ARG; }
-    mode &= GA_DO_ALL;
-    if (mode == 0) { set_error("ga_k_ingest: empty mode"); return GA_ERR_ARG; }
-    if ((mode & GA_DO_CONVERT) && !d_samples) { set_error("ga_k_ingest: GA_DO_CONVERT needs d_samples"); return GA_ERR_ARG; }
-    if ((reinterpret_cast<uintptr_t>(d_pcm) & 15u) || (reinterpret_cast<uintptr_t>(d_samples) & 15u) ||
-        (reinterpret_cast<uintptr_t>(d_results) & 15u) || (reinterpret_cast<uintptr_t>(d_desc) & 15u)) {
-        set_error("ga_k_ingest: device pointers must be 16-byte aligned");
-        return GA_ERR_ARG;
-    }
+    int rc = check_ingest_args("ga_k_ingest", d_pcm, d_desc, d_samples, d_results, mode);
+    if (rc) return rc;
     IngestParams p;
     p.pcm = static_cast<const uint8_t *>(d_pcm);
     p.desc = d_desc;
@@ -423,34 +489,66 @@ extern "C" int ga_k_ingest(const void *d_pcm, const ga_desc *d_desc, uint32_t n_
     p.vad = vad_threshold;
     p.n_msgs = n_msgs;
     p.n_tiles = (n_msgs + 31) / 32;
+    p.msg_bytes = 0;
+    CUtensorMap none;
+    memset(&none, 0, sizeof none);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    // Tuning variants for experiments (GA_INGEST_VARIANT=1..): the three bench modes only.
-    static const int variant = [] { const char *e = getenv("GA_INGEST_VARIANT"); return e ? atoi(e) : 0; }();
-    if (variant && (mode == 3 || mode == 4 || mode == 7)) {
-#define GA_V(ch, stg, coop)                                                 \
-        (mode == 3 ? launch_ingest<ch, stg, 3, coop>(p, st)                 \
-                   : mode == 4 ? launch_ingest<ch, stg, 4, coop>(p, st)     \
-                               : launch_ingest<ch, stg, 7, coop>(p, st))
-        switch (variant) {
-            case 1: return GA_V(128, 3, 0);
-            case 2: return GA_V(128, 3, 1);
-            case 3: return GA_V(128, 2, 1);
-            case 4: return GA_V(256, 2, 0);
-            case 5: return GA_V(256, 2, 1);
-            case 6: return GA_V(128, 4, 1);
-            default: break;
-        }
-#undef GA_V
-    }
     // Defaults from the tuning sweep: lane stores when SHA-256 runs (ALU-bound),
     // the cooperative coalesced store pass otherwise (HBM-bound).
     switch (mode) {
-        case 1: return launch_ingest<128, 2, 1, 1>(p, st);
-        case 2: return launch_ingest<128, 2, 2, 1>(p, st);
-        case 3: return launch_ingest<128, 2, 3, 1>(p, st);
-        case 4: return launch_ingest<128, 3, 4, 0>(p, st);
-        case 5: return launch_ingest<128, 2, 5, 0>(p, st);
-        case 6: return launch_ingest<128, 2, 6, 0>(p, st);
-        default: return launch_ingest<128, 2, 7, 0>(p, st);
+        case 1: return launch_ingest<128, 2, 1, 1>(p, none, st);
+        case 2: return launch_ingest<128, 2, 2, 1>(p, none, st);
+        case 3: return launch_ingest<128, 2, 3, 1>(p, none, st);
+        case 4: return launch_ingest<128, 3, 4, 0>(p, none, st);
+        case 5: return launch_ingest<128, 2, 5, 0>(p, none, st);
+        case 6: return launch_ingest<128, 2, 6, 0>(p, none, st);
+        default: return launch_ingest<128, 2, 7, 0>(p, none, st);
+    }
+}
+
+extern "C" int ga_k_ingest_uniform(const void *d_pcm, const ga_desc *d_desc, uint32_t n_msgs,
+                                   uint64_t first_in_off, uint32_t msg_bytes, uint64_t msg_stride,
+                                   float *d_samples, ga_result *d_results, ga_frame *d_frames,
+                                   uint32_t mode, double vad_threshold, void *stream)
+{
+    using namespace ga;
+    if (n_msgs == 0) return GA_OK;
+    int rc = check_ingest_args("ga_k_ingest_uniform", d_pcm, d_desc, d_samples, d_results, mode);
+    if (rc) return rc;
+    if ((first_in_off & 15u) || (msg_stride & 15u) || msg_stride < msg_bytes || msg_stride >= (1ull << 40) || msg_bytes == 0) {
+        set_error("ga_k_ingest_uniform: offset and stride must be multiples of 16, stride >= msg_bytes > 0");
+        return GA_ERR_ARG;
+    }
+    encode_tiled_fn encode = get_encode_tiled();
+    if (!encode) { set_error("ga_k_ingest_uniform: cuTensorMapEncodeTiled is not available from this driver"); return GA_ERR_CUDA; }
+    CUtensorMap tmap;
+    const cuuint64_t dims[2] = {msg_bytes, n_msgs};                 // [byte within message][message]
+    const cuuint64_t strides[1] = {msg_stride};                     // bytes between consecutive messages
+    const cuuint32_t box[2] = {128, 32};                            // one warp tile slice
+    const cuuint32_t estr[2] = {1, 1};
+    void *base = const_cast<uint8_t *>(static_cast<const uint8_t *>(d_pcm)) + first_in_off;
+    CUresult cr = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, base, dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                         CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (cr != CUDA_SUCCESS) { set_error("ga_k_ingest_uniform: cuTensorMapEncodeTiled failed (%d)", static_cast<int>(cr)); return GA_ERR_CUDA; }
+    IngestParams p;
+    p.pcm = static_cast<const uint8_t *>(d_pcm);
+    p.desc = d_desc;
+    p.samples = d_samples;
+    p.results = d_results;
+    p.frames = d_frames;
+    p.vad = vad_threshold;
+    p.n_msgs = n_msgs;
+    p.n_tiles = (n_msgs + 31) / 32;
+    p.msg_bytes = msg_bytes;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    switch (mode) {
+        case 1: return launch_ingest<128, 2, 1, 5>(p, tmap, st);
+        case 2: return launch_ingest<128, 2, 2, 5>(p, tmap, st);
+        case 3: return launch_ingest<128, 2, 3, 5>(p, tmap, st);
+        case 4: return launch_ingest<128, 3, 4, 4>(p, tmap, st);
+        case 5: return launch_ingest<128, 2, 5, 4>(p, tmap, st);
+        case 6: return launch_ingest<128, 2, 6, 4>(p, tmap, st);
+        default: return launch_ingest<128, 2, 7, 4>(p, tmap, st);
     }
 }

@@ -286,6 +286,34 @@ def test_cfg3_collision_groups_winners_match_cpu_baseline(ctx):
     assert ((s2[:, -1] - s2[:, -2]) / s2[:, -1] > 1e-3).all()
 
 
+@pytest.mark.parametrize("msg_bytes", [640, 128, 64, 16, 641 + 15, 3840, 1000 - 1000 % 16])
+def test_uniform_batches_through_the_tensor_map_path(msg_bytes):
+    """Equal-sized chunks back to back in the ring are staged with one 2-D TMA copy per 32 messages
+    (ga_k_ingest_uniform, picked automatically by ga_submit); a context forced to per-message bulk
+    copies must give byte-identical records and samples, and both must match the oracle."""
+    rng = np.random.default_rng(msg_bytes)
+    n = 333                                               # not a multiple of 32: partial last tile
+    chunks = [rng.integers(0, 256, size=msg_bytes, dtype=np.uint8).tobytes() for _ in range(n)]
+    sid = np.arange(n, dtype=np.uint32) % 50
+    fl = np.where(np.arange(n) < 50, L.MSG_FIRST, 0).astype(np.uint32)
+    out = {}
+    for staging in (L.STAGING_AUTO, L.STAGING_BULK):
+        with api.Context(max_streams=64, max_batch_msgs=512, ring_bytes=4 << 20, arena_samples=32_000,
+                         wake_samples_max=64, mode=L.DO_ALL, want_frames=True, staging=staging) as c:
+            res, frames = c.ingest(chunks, sid, fl)
+            out[staging] = (res.copy(), frames.copy(), [c.fetch_samples(s) for s in range(50)])
+    a, b = out[L.STAGING_AUTO], out[L.STAGING_BULK]
+    assert a[0].tobytes() == b[0].tobytes() and a[1].tobytes() == b[1].tobytes()
+    for x, y in zip(a[2], b[2]):
+        assert np.array_equal(bits(x), bits(y))
+    fpos = 0
+    for i in range(0, n, 7):
+        nf = (msg_bytes // 2 + 319) // 320
+        check_message(a[0][i], chunks[i], a[1][i * nf:(i + 1) * nf])
+    want0 = np.concatenate([ora.bytes_to_float32(chunks[i])[0] for i in range(n) if sid[i] == 0])
+    assert np.array_equal(bits(a[2][0]), bits(want0))
+
+
 def test_mode_subsets_agree_with_the_fused_kernel():
     rng = np.random.default_rng(9)
     chunks = [rng.integers(0, 256, size=int(n), dtype=np.uint8).tobytes()
