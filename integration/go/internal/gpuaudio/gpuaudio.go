@@ -1,0 +1,106 @@
+// Package gpuaudio binds libgpuaudio.so (include/gpuaudio.h) for loqa-hub.
+// Written against the header; NOT compiled in the authoring image (no Go toolchain there).
+// See INTEGRATION.md for the call-site changes in internal/grpc/audio_service.go.
+package gpuaudio
+
+/*
+#cgo CFLAGS:  -I${SRCDIR}/../../third_party/gpuaudio/include
+#cgo LDFLAGS: -L${SRCDIR}/../../third_party/gpuaudio/lib -lgpuaudio
+#include <stdlib.h>
+#include "gpuaudio.h"
+*/
+import "C"
+
+import (
+	"errors"
+	"unsafe"
+)
+
+type Ctx struct{ c *C.ga_ctx }
+
+type Config struct {
+	Device                     int
+	MaxStreams, MaxBatchMsgs   uint32
+	RingBytes                  uint64
+	ArenaSamples, WakeSamples  uint64
+}
+
+func lastErr(rc C.int) error { return errors.New(C.GoString(C.ga_last_error())) }
+
+// New is called beside createAudioService (audio_service.go:233-244).
+func New(cfg Config) (*Ctx, error) {
+	cc := C.ga_config{device: C.int32_t(cfg.Device), max_streams: C.uint32_t(cfg.MaxStreams),
+		max_batch_msgs: C.uint32_t(cfg.MaxBatchMsgs), max_inflight: 4,
+		ring_bytes: C.uint64_t(cfg.RingBytes), arena_samples: C.uint64_t(cfg.ArenaSamples),
+		wake_samples_max: C.uint64_t(cfg.WakeSamples), mode: C.GA_DO_ALL, vad_threshold: 0.01}
+	var c *C.ga_ctx
+	if rc := C.ga_init(&cc, &c); rc != 0 {
+		return nil, lastErr(rc)
+	}
+	return &Ctx{c}, nil
+}
+func (x *Ctx) Close() { C.ga_shutdown(x.c) }
+
+// Push copies one chunk.AudioData into the C-owned pinned ring and returns its offset.
+// Called from the per-stream goroutines (StreamAudio, audio_service.go:964 and :999) instead of
+// bytesToFloat32Array; lock-free on the C side.  C never keeps a Go pointer (cgo rule): the
+// destination is C memory, wrapped with unsafe.Slice only for the copy.
+func (x *Ctx) Push(audioData []byte) (uint64, error) {
+	var p unsafe.Pointer
+	var off C.uint64_t
+	if rc := C.ga_ring_reserve(x.c, C.uint64_t(len(audioData)), &p, &off); rc != 0 {
+		return 0, lastErr(rc)
+	}
+	copy(unsafe.Slice((*byte)(p), len(audioData)), audioData)
+	return uint64(off), nil
+}
+
+type Msg = C.ga_msg       // {ring_offset, nbytes, stream_id, flags}
+type Result = C.ga_result // {digest[32], sumsq, rms, n_samples, nonzero, peak, flags}
+
+// Submit is called once per batch tick by the single batching goroutine (never per chunk:
+// a cgo call is an OS-thread hop).  Messages in ring-offset order.
+func (x *Ctx) Submit(msgs []Msg) (uint64, error) {
+	var t C.uint64_t
+	if rc := C.ga_submit(x.c, &msgs[0], C.uint32_t(len(msgs)), &t); rc != 0 {
+		return 0, lastErr(rc)
+	}
+	return uint64(t), nil
+}
+
+// Wait returns a view of the C-owned pinned result records (valid for 4 more Submits).
+func (x *Ctx) Wait(ticket uint64) ([]Result, error) {
+	var r *C.ga_result
+	var n C.uint32_t
+	if rc := C.ga_wait_view(x.c, C.uint64_t(ticket), &r, nil, &n, nil); rc != 0 {
+		return nil, lastErr(rc)
+	}
+	return unsafe.Slice((*Result)(r), int(n)), nil
+}
+
+// Arbitrate replaces the scoring loop of performArbitration (audio_service.go:517-547) for any
+// number of windows.  members are stream slots in JOIN ORDER per window.
+func (x *Ctx) Arbitrate(segOffsets, streamIDs []uint32, statusIn []uint8) (winner []uint32, scores []float64, statusOut []uint8, err error) {
+	nw := len(segOffsets) - 1
+	winner, scores, statusOut = make([]uint32, nw), make([]float64, len(streamIDs)), make([]uint8, len(streamIDs))
+	rc := C.ga_arbitrate(x.c, (*C.uint32_t)(&segOffsets[0]), C.uint32_t(nw), (*C.uint32_t)(&streamIDs[0]),
+		(*C.uint8_t)(&statusIn[0]), (*C.uint32_t)(&winner[0]), (*C.double)(&scores[0]), (*C.uint8_t)(&statusOut[0]))
+	if rc != 0 {
+		err = lastErr(rc)
+	}
+	return
+}
+
+// Samples fetches WakeWordSignal ++ SpeechAudio of one stream (audio_service.go:592-594) — only
+// for the arbitration winner, right before TranscribeWithConfidence (:609).
+func (x *Ctx) Samples(stream uint32) ([]float32, error) {
+	var n, w C.uint64_t
+	C.ga_stream_info(x.c, C.uint32_t(stream), &n, &w)
+	out := make([]float32, int(n))
+	if n > 0 {
+		if rc := C.ga_fetch_samples(x.c, C.uint32_t(stream), 0, n, (*C.float)(&out[0])); rc != 0 {
+			return nil, lastErr(rc)
+		}
+	}
+	return out, nil
+}
