@@ -21,9 +21,10 @@
 namespace ga {
 
 constexpr int kArbWarps = 1;                    // 4,096 members are only 128 tiles: one warp per block spreads them over the SMs
-constexpr int kArbSlice = 512;                  // bytes of f32 per member per stage
-constexpr int kArbStages = 4;                   // deep enough that a lane's add chain never waits for the copy
-constexpr int kArbRowStride = kArbSlice + 16;   // 33 x 16 B: conflict-free lane-per-row LDS.128
+constexpr int kArbSlice = 2048;                 // bytes of f32 per member per stage: per-lane bulk copies are issued
+                                                // one at a time (~60 cycles each), so few and large
+constexpr int kArbStages = 3;
+constexpr int kArbRowStride = kArbSlice + 16;   // 129 x 16 B (odd): conflict-free lane-per-row LDS.128
 constexpr int kArbStageBytes = 32 * kArbRowStride;
 constexpr int kArbWarpBytes = kArbStages * kArbStageBytes + 128;
 
@@ -87,9 +88,17 @@ score_tiles(const float *__restrict__ samples, const uint64_t *__restrict__ wake
                 const uint32_t cnt = min(n - lo, static_cast<uint32_t>(kArbSlice / 4));
                 const float4 *row = reinterpret_cast<const float4 *>(wbase + stage * kArbStageBytes + lane * kArbRowStride);
                 uint32_t k = 0;
-                for (; k + 4 <= cnt; k += 4) {
-                    const float4 v = row[k >> 2];
-                    add(v.x); add(v.y); add(v.z); add(v.w);
+                if (!stats) {
+                    // arbitration needs only the sum: multiply, widen, add — nothing else per sample
+                    for (; k + 4 <= cnt; k += 4) {
+                        const float4 v = row[k >> 2];
+                        sum += sq_f64(v.x); sum += sq_f64(v.y); sum += sq_f64(v.z); sum += sq_f64(v.w);
+                    }
+                } else {
+                    for (; k + 4 <= cnt; k += 4) {
+                        const float4 v = row[k >> 2];
+                        add(v.x); add(v.y); add(v.z); add(v.w);
+                    }
                 }
                 if (k < cnt) {
                     const float4 v = row[k >> 2];
