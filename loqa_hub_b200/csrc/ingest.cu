@@ -19,9 +19,9 @@
 //             lanes (L2 merges the sectors), but it needs no second pass, no shuffles and only
 //             one division per sample — best when the kernel is bound by the integer ALU pipe,
 //             i.e. whenever SHA-256 runs (measured 1.20 ms vs 1.36 ms per 20,480 audio-s).
-//   COOP = 1  a warp-cooperative pass converts the slice again with 4 samples per lane and
-//             writes 256 contiguous bytes per row — best for the HBM-bound instantiations
-//             without SHA-256 (0.43 ms vs 0.91 ms).
+//   COOP = 1  the lane writes its samples to a padded f32 tile in shared memory and a
+//             warp-cooperative pass copies the tile out, 256 contiguous bytes per row per
+//             instruction — best for the HBM-bound instantiations without SHA-256.
 // A third variant staged the samples in shared memory and used TMA bulk stores; with 128-256 B
 // per store and the proxy fence it was slower than both (tuning log).
 // Staging has two forms (bit 2 of COOP).  Generic batches (ragged lengths, arbitrary offsets):
@@ -44,14 +44,20 @@ namespace ga {
 
 constexpr int kWarpsPerBlock = 4;
 
-template <int CH, int STAGES, bool TMAP = false>
+template <int CH, int STAGES, bool TMAP = false, bool OUT_TILE = false>
 struct TileSmem {
     // generic: rows padded by 16 B ((CH/16 + 1) odd -> conflict-free LDS.128);
     // tensor-map: dense 128-byte rows, 128B-swizzled by the TMA unit, stages 1024-byte aligned
     static constexpr int kRowStride = TMAP ? CH : CH + 16;
     static constexpr int kStageBytes = 32 * kRowStride;
-    static constexpr int kBarBase = STAGES * kStageBytes;
-    static constexpr int kWarpBytes = kBarBase + (TMAP ? 1024 : 128);   // + barriers (padded)
+    // optional f32 output tile (one slice of every row, rows padded by 16 B: conflict-free
+    // lane-per-row STS.128) followed by the tile's 32 output offsets
+    static constexpr int kOutRowStride = 2 * CH + 16;
+    static constexpr int kOutBase = STAGES * kStageBytes;
+    static constexpr int kOutBytes = OUT_TILE ? 32 * kOutRowStride + 256 : 0;
+    static constexpr int kBarBase = kOutBase + kOutBytes;
+    static constexpr int kRawBytes = kBarBase + 128;
+    static constexpr int kWarpBytes = TMAP ? ((kRawBytes + 1023) / 1024) * 1024 : kRawBytes;   // stages stay 1024-aligned
     static_assert(!TMAP || CH == 128, "the swizzled layout is written for 128-byte slices");
     static_assert(CH % 64 == 0, "slices must hold whole SHA-256 blocks");
     static_assert(((CH / 16) + 1) % 2 == 1, "row stride must be an odd number of 16-byte units");
@@ -131,7 +137,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 ingest_kernel(const IngestParams p, const __grid_constant__ CUtensorMap tmap)
 {
     constexpr bool kTmap = (COOP & 4) != 0;                                       // 2-D TMA staging (uniform batches)
-    using L = TileSmem<CH, STAGES, kTmap>;
+    constexpr bool kOutTile = (MODE & GA_DO_CONVERT) != 0 && (COOP & 1) == 1;
+    using L = TileSmem<CH, STAGES, kTmap, kOutTile>;
     constexpr bool kCoop = (MODE & GA_DO_CONVERT) != 0 && (COOP & 1) == 1;      // cooperative store pass
     constexpr bool kLaneStore = (MODE & GA_DO_CONVERT) != 0 && (COOP & 1) == 0; // lane stores its own samples
     constexpr bool kFeat = (MODE & GA_DO_FEATURES) != 0;
@@ -256,41 +263,16 @@ ingest_kernel(const IngestParams p, const __grid_constant__ CUtensorMap tmap)
             const uint32_t lo = c * CH;
             mbar_wait(&bars[stage], parity);
 
-            // ---------------- cooperative convert + coalesced store (COOP = 1)
-            if (kCoop) {
-                constexpr int VPR = CH / 8;   // 4-sample vectors per row slice
-#pragma unroll 4
-                for (int k = 0; k < VPR; k++) {
-                    const int v = k * 32 + lane;
-                    const int row = v / VPR, col = v % VPR;
-                    const uint32_t r_even = __shfl_sync(FULL, nb_even, row);
-                    const uint64_t r_out = __shfl_sync(FULL, out_off, row);
-                    const uint32_t byte0 = lo + col * 8;
-                    if (byte0 < r_even) {
-                        const uint2 raw = *reinterpret_cast<const uint2 *>(row_addr<kTmap, L::kRowStride>(sbase, row, col * 8));
-                        float v0, v1, v2, v3;
-                        unpack2(raw.x, v0, v1);
-                        unpack2(raw.y, v2, v3);
-                        const float f0 = pcm_to_f32(v0), f1 = pcm_to_f32(v1);
-                        const float f2 = pcm_to_f32(v2), f3 = pcm_to_f32(v3);
-                        float *dst = p.samples + r_out + (byte0 >> 1);
-                        const uint32_t nvalid = (r_even - byte0) >> 1;
-                        if (nvalid >= 4 && (r_out & 3ull) == 0) {
-                            st_global_v4(dst, f0, f1, f2, f3);
-                        } else {
-                            dst[0] = f0;
-                            if (nvalid > 1) dst[1] = f1;
-                            if (nvalid > 2) dst[2] = f2;
-                            if (nvalid > 3) dst[3] = f3;
-                        }
-                    }
-                }
-            }
-
             // ---------------- lane = message.  One loop over the 64-byte blocks this slice
             // contributes, including the padding block(s) when the message ends here, so the
             // unrolled compression exists once in the instruction stream.
-            if ((kFeat || kSha || kLaneStore) && c < my_nch) {
+            float *orow = reinterpret_cast<float *>(wbase + L::kOutBase + lane * L::kOutRowStride);
+            if (kCoop) {
+                const uint32_t hi_even = min(nb_even, lo + CH);
+                const uint64_t ns = (c < my_nch && hi_even > lo) ? (hi_even - lo) >> 1 : 0;
+                reinterpret_cast<uint64_t *>(wbase + L::kOutBase + 32 * L::kOutRowStride)[lane] = (out_off & 0xFFFFFFFFFFFFull) | (ns << 48);
+            }
+            if ((kFeat || kSha || kLaneStore || kCoop) && c < my_nch) {
                 const uint32_t span = min(nb, lo + CH) - lo;
                 const uint32_t nfull = span >> 6;
                 const uint32_t rem = span & 63u;
@@ -309,10 +291,14 @@ ingest_kernel(const IngestParams p, const __grid_constant__ CUtensorMap tmap)
 #pragma unroll
                         for (int j = 0; j < 16; j++) w[j] = 0;
                     }
-                    if (kFeat || kLaneStore) {
+                    if (kFeat || kLaneStore || kCoop) {
                         if (vb == 64) {
                             float *g = p.samples + out_off + (lo >> 1) + b * 32;
                             const bool galigned = (out_off & 3ull) == 0;
+                            // stage 1: 32 independent conversions (and squares); stage 2: the two
+                            // strictly ordered float64 chains — written apart so the scheduler can
+                            // overlap the conversions of one word with the additions of another
+                            float sqf[32];
 #pragma unroll
                             for (int j = 0; j < 16; j += 2) {
                                 float v0, v1, v2, v3;
@@ -320,14 +306,25 @@ ingest_kernel(const IngestParams p, const __grid_constant__ CUtensorMap tmap)
                                 unpack2(w[j + 1], v2, v3);
                                 const float x0 = pcm_to_f32(v0), x1 = pcm_to_f32(v1);
                                 const float x2 = pcm_to_f32(v2), x3 = pcm_to_f32(v3);
-                                if (kLaneStore) {
+                                if (kCoop) {
+                                    *reinterpret_cast<float4 *>(orow + b * 32 + 2 * j) = make_float4(x0, x1, x2, x3);
+                                } else if (kLaneStore) {
                                     if (galigned) st_global_v4(g + 2 * j, x0, x1, x2, x3);
                                     else { g[2 * j] = x0; g[2 * j + 1] = x1; g[2 * j + 2] = x2; g[2 * j + 3] = x3; }
                                 }
                                 if (kFeat) {
-                                    chain(x0); chain(x1); chain(x2); chain(x3);
+                                    sqf[2 * j] = __fmul_rn(x0, x0); sqf[2 * j + 1] = __fmul_rn(x1, x1);
+                                    sqf[2 * j + 2] = __fmul_rn(x2, x2); sqf[2 * j + 3] = __fmul_rn(x3, x3);
                                     frm.stats_word(w[j]);
                                     frm.stats_word(w[j + 1]);
+                                }
+                            }
+                            if (kFeat) {
+#pragma unroll
+                                for (int i = 0; i < 32; i++) {
+                                    const double q = static_cast<double>(sqf[i]);
+                                    msg_sum += q;
+                                    frm.sum += q;
                                 }
                             }
                             if (kFeat) {
@@ -342,7 +339,8 @@ ingest_kernel(const IngestParams p, const __grid_constant__ CUtensorMap tmap)
                                 float v0, v1;
                                 unpack2(h, v0, v1);
                                 const float x0 = pcm_to_f32(v0);
-                                if (kLaneStore) p.samples[out_off + (lo >> 1) + b * 32 + k] = x0;
+                                if (kCoop) orow[b * 32 + k] = x0;
+                                else if (kLaneStore) p.samples[out_off + (lo >> 1) + b * 32 + k] = x0;
                                 if (kFeat) {
                                     chain(x0);
                                     frm.stats_word(h);              // upper half is a zero sample: neutral
@@ -381,6 +379,36 @@ ingest_kernel(const IngestParams p, const __grid_constant__ CUtensorMap tmap)
 
             __syncwarp();          // every lane is done reading this stage
             produce(stage);        // refill it with the slice STAGES jobs ahead
+
+            // ---------------- cooperative copy-out of the f32 tile (COOP bit 0): the lanes wrote their
+            // rows above; now 16 lanes cover one row's 256 contiguous bytes per instruction
+            if (kCoop) {
+                constexpr int VPR = CH / 8;   // 16-byte vectors (4 samples) per row slice
+                const uint64_t *otab = reinterpret_cast<const uint64_t *>(wbase + L::kOutBase + 32 * L::kOutRowStride);
+#pragma unroll 4
+                for (int k = 0; k < VPR; k++) {
+                    const int v = k * 32 + lane;
+                    const int row = v / VPR, col = v % VPR;
+                    const uint64_t packed = otab[row];                 // out_off (48 bits) | valid samples of the row in this slice
+                    const uint64_t r_out = packed & 0xFFFFFFFFFFFFull;
+                    const uint32_t r_ns = static_cast<uint32_t>(packed >> 48);   // valid samples of the row in this slice (<= CH/2)
+                    const uint32_t s0 = col * 4;
+                    if (s0 < r_ns) {
+                        const float4 t = *reinterpret_cast<const float4 *>(wbase + L::kOutBase + row * L::kOutRowStride + col * 16);
+                        float *dst = p.samples + r_out + (lo >> 1) + s0;
+                        const uint32_t nvalid = r_ns - s0;
+                        if (nvalid >= 4 && (r_out & 3ull) == 0) {
+                            st_global_v4(dst, t.x, t.y, t.z, t.w);
+                        } else {
+                            dst[0] = t.x;
+                            if (nvalid > 1) dst[1] = t.y;
+                            if (nvalid > 2) dst[2] = t.z;
+                            if (nvalid > 3) dst[3] = t.w;
+                        }
+                    }
+                }
+                __syncwarp();      // the tile is free for the next slice
+            }
         }
 
         // ---------------- result record
@@ -412,7 +440,7 @@ ingest_kernel(const IngestParams p, const __grid_constant__ CUtensorMap tmap)
 template <int CH, int STAGES, uint32_t MODE, int COOP>
 static int launch_ingest(const IngestParams &p, const CUtensorMap &tmap, cudaStream_t st)
 {
-    using L = TileSmem<CH, STAGES, (COOP & 4) != 0>;
+    using L = TileSmem<CH, STAGES, (COOP & 4) != 0, (MODE & GA_DO_CONVERT) != 0 && (COOP & 1) == 1>;
     constexpr int smem = kWarpsPerBlock * L::kWarpBytes;
     auto kern = ingest_kernel<CH, STAGES, MODE, COOP>;
     static thread_local int configured_dev = -1;
