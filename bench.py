@@ -42,6 +42,11 @@ WORKLOADS = {
     "cfg5": dict(groups=1024, group_size=8, n_msgs=250, msg_samples=320, wake_msgs=15,
                  desc="configs[4] shard: 8,192 streams per GPU (65,536 over 8), cross-shard windows"),
 }
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
+# `ncu --set full` captures (profiles/r1_ncu_summary.md) at the default cfg3 size; None where no
+# capture exists for that variant.  Not measured live: a run under a profiler is never timed.
+NCU_TRAFFIC_BYTES = {("cfg3", "fused", "tmap"): 2_015_968_616, ("cfg3", "split", "tmap"): 2_006_581_592}
+NCU_ALU_PIPE_PCT = {("cfg3", "fused", "tmap"): 82.8}
 # HBM bytes per audio-second with f32 samples materialised
 ALGO_BYTES_PER_AUDIO_S = 32_000 + 64_000 + 50 * 64
 ALGO_BYTES_PER_AUDIO_S_48K = 192_000 + 64_000 + 50 * 64
@@ -409,10 +414,14 @@ def main():
                        "l2": "inputs %.0f MB + outputs %.0f MB per step > 126 MB L2, no flush needed" % (
                            n_msgs * ms * 2 / 1e6, n_msgs * (ms * 4 + 64) / 1e6)},
             "roofline": {"bound": "hbm", "kernel": "ingest_kernel<%s>" % ("sha256 of 48 kHz bytes" if fmt48 else args.mode), "achieved": achieved,
-                         "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": NCU_TRAFFIC_BYTES.get((args.workload, args.mode, args.staging)),
+                         "alu_pipe_pct_of_peak_ncu": NCU_ALU_PIPE_PCT.get((args.workload, args.mode, args.staging)),
                          "peak_source": peak_src, "ms_per_launch": ingest_ms,
                          "algorithmic_bytes_per_launch": algo_bytes,
-                         "note": "fused kernel is bound by the integer ALU pipe (SHA-256), see profiles/"},
+                         "note": "the fused kernel is bound by the integer ALU pipe (SHA-256), not by HBM: see "
+                                 "alu_pipe_pct_of_peak_ncu and profiles/r1_ncu_summary.md; traffic is per launch "
+                                 "from the committed ncu capture"},
             "gpu_launches": int(launches),
             "clocks": clk.summary(),
         }

@@ -314,6 +314,50 @@ def test_uniform_batches_through_the_tensor_map_path(msg_bytes):
     assert np.array_equal(bits(a[2][0]), bits(want0))
 
 
+def test_full_size_cfg3_batch_matches_the_cpu_baseline_exactly():
+    """BASELINE.json configs[2] at FULL size — 4,096 streams x 250 chunks = 1,024,000 messages,
+    655 MB of PCM — in one launch of the fused kernel: every digest, every wake-word score and every
+    winner against the multi-threaded CPU baseline, plus a checksum of the converted samples."""
+    import torch
+    dev = torch.device("cuda", 0)
+    S, gs, M, ms, wake = 4096, 8, 250, 320, 15
+    pcm_host = api.synth_batch_host(synth.SEED, 0, S, gs, M, ms, n_threads=16)
+    _, dg, wn, sc = ora.cpu_baseline(pcm_host.view(np.uint8), S, M, ms * 2, wake, gs, 16, want_outputs=True)
+    pcm = torch.from_numpy(pcm_host).to(dev)
+    n = S * M
+    k = np.arange(n, dtype=np.uint64)
+    arena = M * ms
+    descs = api.make_descs(k * (ms * 2), np.full(n, ms * 2, np.uint32), (k % S) * arena + (k // S) * ms,
+                           (k % S).astype(np.uint32), frame_off=np.zeros(n, np.uint32))
+    d_desc = torch.from_numpy(descs.view(np.uint8)).to(dev)
+    samples = torch.empty(S * arena + 4, dtype=torch.float32, device=dev)
+    results = torch.empty(n * 64, dtype=torch.uint8, device=dev)
+    api.k_ingest_uniform(pcm.data_ptr(), d_desc.data_ptr(), n, 0, ms * 2, ms * 2, samples.data_ptr(), results.data_ptr())
+    off = torch.arange(S, dtype=torch.int64, device=dev) * arena
+    cnt = torch.full((S,), wake * ms, dtype=torch.int32, device=dev)
+    st = torch.full((S,), L.RELAY_CONTENDING, dtype=torch.uint8, device=dev)
+    seg = torch.arange(0, S + 1, gs, dtype=torch.int32, device=dev)
+    scores = torch.zeros(S, dtype=torch.float64, device=dev)
+    winner = torch.zeros(S // gs, dtype=torch.int32, device=dev)
+    st_out = torch.zeros(S, dtype=torch.uint8, device=dev)
+    api.k_arbitrate(samples.data_ptr(), off.data_ptr(), cnt.data_ptr(), st.data_ptr(), seg.data_ptr(), S // gs, S,
+                    scores.data_ptr(), winner.data_ptr(), st_out.data_ptr())
+    torch.cuda.synchronize()
+    res = results.cpu().numpy().view(L.RESULT_DTYPE).reshape(M, S)
+    assert np.array_equal(res["digest"], dg)                                  # 1,024,000 digests
+    assert np.array_equal(scores.cpu().numpy(), sc)                           # float64, bit for bit
+    assert np.array_equal(winner.cpu().numpy().astype(np.int64), np.arange(0, S, gs) + wn)
+    # samples: conversion is a pure function of the int16 value, so a per-value table gives the exact answer
+    table = ora.bytes_to_float32(np.arange(-32768, 32768, dtype=np.int32).astype("<i2").tobytes())[0]
+    for s_id in (0, 1234, 4095):
+        want = table[pcm_host.reshape(M, S, ms)[:, s_id, :].reshape(-1).astype(np.int32) + 32768]
+        got = samples[s_id * arena:(s_id + 1) * arena].cpu().numpy()
+        assert np.array_equal(bits(got), bits(want))
+    total = samples[:S * arena].double().sum().item()
+    want_total = float(table.astype(np.float64)[pcm_host.astype(np.int32) + 32768].sum())
+    assert abs(total - want_total) <= 1e-9 * max(1.0, abs(want_total)) + 1e-3   # order-independent checksum
+
+
 def test_mode_subsets_agree_with_the_fused_kernel():
     rng = np.random.default_rng(9)
     chunks = [rng.integers(0, 256, size=int(n), dtype=np.uint8).tobytes()
