@@ -8,7 +8,7 @@ CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libgpuaudio.so")
 SOURCES = ["ingest.cu", "arbitrate.cu", "resample.cu", "utterance.cu", "context.cu", "hub.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+FLAGS = os.environ.get("GA_NVCC_EXTRA", "").split() + ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-shared", "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function", "-cudart", "static",
          "--threads", "0"]
 
