@@ -83,6 +83,8 @@ struct ga_ctx {
     std::vector<ga::Slot> slots;
     uint64_t next_ticket = 1, oldest_ticket = 1;
     cudaEvent_t prev_kdone = nullptr;
+    uint8_t *d_arb = nullptr;                  // grow-only device scratch of ga_arbitrate (no per-call cudaMalloc)
+    size_t arb_bytes = 0;
     std::mutex mu;   // guards submit/wait/arbitrate bookkeeping (not the ring reserve path)
     // scratch for ga_arbitrate
     cudaStream_t aux = nullptr;
@@ -122,6 +124,7 @@ static void destroy(ga_ctx *c)
     if (c->d_arena) cudaFree(c->d_arena);
     if (c->d_hist) cudaFree(c->d_hist);
     if (c->d_sha) cudaFree(c->d_sha);
+    if (c->d_arb) cudaFree(c->d_arb);
     delete c;
 }
 
@@ -717,31 +720,45 @@ extern "C" int ga_arbitrate(ga_ctx *ctx, const uint32_t *seg_offsets, uint32_t n
         off[m] = static_cast<uint64_t>(stream_ids[m]) * ctx->cfg.arena_samples;
         cnt[m] = static_cast<uint32_t>(ctx->streams[stream_ids[m]].wake_n);
     }
-    DevBuf d_off, d_cnt, d_st, d_seg, d_sc, d_win, d_so;
-    if ((rc = d_off.alloc(8ull * n_members)) || (rc = d_cnt.alloc(4ull * n_members)) || (rc = d_st.alloc(n_members)) ||
-        (rc = d_seg.alloc(4ull * (n_windows + 1))) || (rc = d_sc.alloc(8ull * n_members)) ||
-        (rc = d_win.alloc(4ull * n_windows)) || (rc = d_so.alloc(n_members)))
-        return rc;
+    // device arrays carved from one grow-only scratch allocation owned by the context
+    auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
+    const size_t o_off = 0, o_cnt = o_off + up(8ull * n_members), o_st = o_cnt + up(4ull * n_members),
+                 o_seg = o_st + up(n_members), o_sc = o_seg + up(4ull * (n_windows + 1)),
+                 o_win = o_sc + up(8ull * n_members), o_so = o_win + up(4ull * n_windows),
+                 need = o_so + up(n_members) + 256;
     cudaStream_t s = ctx->aux;
+    if (need > ctx->arb_bytes) {
+        GA_CUDA_TRY(cudaStreamSynchronize(s));
+        if (ctx->d_arb) cudaFree(ctx->d_arb);
+        ctx->d_arb = nullptr; ctx->arb_bytes = 0;
+        const size_t want = need + need / 2;
+        cudaError_t e = cudaMalloc(reinterpret_cast<void **>(&ctx->d_arb), want);
+        if (e != cudaSuccess) { cudaGetLastError(); set_error("ga_arbitrate: cudaMalloc(%zu) failed: %s", want, cudaGetErrorString(e)); return GA_ERR_NOMEM; }
+        ctx->arb_bytes = want;
+    }
+    uint8_t *b = ctx->d_arb;
+    uint64_t *d_off = reinterpret_cast<uint64_t *>(b + o_off);
+    uint32_t *d_cnt = reinterpret_cast<uint32_t *>(b + o_cnt), *d_seg = reinterpret_cast<uint32_t *>(b + o_seg),
+             *d_win = reinterpret_cast<uint32_t *>(b + o_win);
+    uint8_t *d_st = b + o_st, *d_so = b + o_so;
+    double *d_sc = reinterpret_cast<double *>(b + o_sc);
     rc = join_inflight(ctx, s);
     if (rc) return rc;
     if (n_members) {
-        GA_CUDA_TRY(cudaMemcpyAsync(d_off.p, off.data(), 8ull * n_members, cudaMemcpyHostToDevice, s));
-        GA_CUDA_TRY(cudaMemcpyAsync(d_cnt.p, cnt.data(), 4ull * n_members, cudaMemcpyHostToDevice, s));
-        GA_CUDA_TRY(cudaMemcpyAsync(d_st.p, status_in, n_members, cudaMemcpyHostToDevice, s));
+        GA_CUDA_TRY(cudaMemcpyAsync(d_off, off.data(), 8ull * n_members, cudaMemcpyHostToDevice, s));
+        GA_CUDA_TRY(cudaMemcpyAsync(d_cnt, cnt.data(), 4ull * n_members, cudaMemcpyHostToDevice, s));
+        GA_CUDA_TRY(cudaMemcpyAsync(d_st, status_in, n_members, cudaMemcpyHostToDevice, s));
         // scores of skipped relays stay what the caller passed in (audio_service.go:522-524)
-        GA_CUDA_TRY(cudaMemcpyAsync(d_sc.p, scores, 8ull * n_members, cudaMemcpyHostToDevice, s));
+        GA_CUDA_TRY(cudaMemcpyAsync(d_sc, scores, 8ull * n_members, cudaMemcpyHostToDevice, s));
     }
-    GA_CUDA_TRY(cudaMemcpyAsync(d_seg.p, seg_offsets, 4ull * (n_windows + 1), cudaMemcpyHostToDevice, s));
-    rc = ga_k_arbitrate(ctx->d_arena, d_off.as<uint64_t>(), d_cnt.as<uint32_t>(), d_st.as<uint8_t>(),
-                        d_seg.as<uint32_t>(), n_windows, n_members, d_sc.as<double>(), d_win.as<uint32_t>(),
-                        d_so.as<uint8_t>(), s);
+    GA_CUDA_TRY(cudaMemcpyAsync(d_seg, seg_offsets, 4ull * (n_windows + 1), cudaMemcpyHostToDevice, s));
+    rc = ga_k_arbitrate(ctx->d_arena, d_off, d_cnt, d_st, d_seg, n_windows, n_members, d_sc, d_win, d_so, s);
     if (rc) return rc;
     if (n_members) {
-        GA_CUDA_TRY(cudaMemcpyAsync(scores, d_sc.p, 8ull * n_members, cudaMemcpyDeviceToHost, s));
-        GA_CUDA_TRY(cudaMemcpyAsync(status_out, d_so.p, n_members, cudaMemcpyDeviceToHost, s));
+        GA_CUDA_TRY(cudaMemcpyAsync(scores, d_sc, 8ull * n_members, cudaMemcpyDeviceToHost, s));
+        GA_CUDA_TRY(cudaMemcpyAsync(status_out, d_so, n_members, cudaMemcpyDeviceToHost, s));
     }
-    GA_CUDA_TRY(cudaMemcpyAsync(winner_idx, d_win.p, 4ull * n_windows, cudaMemcpyDeviceToHost, s));
+    GA_CUDA_TRY(cudaMemcpyAsync(winner_idx, d_win, 4ull * n_windows, cudaMemcpyDeviceToHost, s));
     GA_CUDA_TRY(cudaStreamSynchronize(s));
     return GA_OK;
 }
