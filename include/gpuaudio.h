@@ -368,6 +368,12 @@ int ga_utterance_digest(ga_ctx *ctx, uint32_t stream_id, uint8_t digest[32], uin
  * ga_k_* arbitration sequence (e.g. with an exchange step between shards) on the context's
  * samples.  Valid until ga_shutdown; wait all tickets before reading. */
 int ga_device_arena(ga_ctx *ctx, void **d_arena);
+/* Fingerprint of a stream's CONVERTED audio: SHA-256 over the little-endian IEEE-754 bytes of
+ * WakeWordSignal ++ SpeechAudio — the byte string the hub itself serialises for STT
+ * (internal/llm/stt_client.go:390-395) and the natural input of the hook whose argument is
+ * []float32 (VoiceEvent.SetAudioMetadata, events/voice_event.go:84-88).  Hashed on the device from
+ * the sample arena; nothing is copied to the host but the digest. */
+int ga_samples_digest(ga_ctx *ctx, uint32_t stream_id, uint8_t digest[32]);
 
 /* performArbitration for many windows (audio_service.go:505-571).  Host arrays:
  * seg_offsets[n_windows+1], stream_ids / status_in / scores / status_out per member,

@@ -68,6 +68,7 @@ SYMBOLS = {
     "ga_k_sha256_chain": (_i32, [_vp, _vp, _vp, _vp, _u32, _vp, _vp]),
     "ga_k_sha256_final": (_i32, [_vp, _vp, _u32, _vp, _vp, _vp]),
     "ga_k_sha256_reset": (_i32, [_vp, _u32, _vp]),
+    "ga_samples_digest": (_i32, [_vp, _u32, _vp]),
     "ga_utterance_digest": (_i32, [_vp, _u32, _vp, C.POINTER(_u64)]),
     "ga_k_resample48": (_i32, [_vp, _vp, _u32, _vp, _vp, _vp, _vp, C.c_double, _vp]),
     "ga_k_ingest_uniform": (_i32, [_vp, _vp, _u32, _u64, _u32, _u64, _vp, _vp, _vp, _u32, C.c_double, _vp]),

@@ -226,6 +226,11 @@ class Context:
         check(load().ga_utterance_digest(self._h, stream_id, ptr(out), C.byref(n)))
         return out.tobytes(), n.value
 
+    def samples_digest(self, stream_id):
+        out = np.zeros(32, dtype=np.uint8)
+        check(load().ga_samples_digest(self._h, stream_id, ptr(out)))
+        return out.tobytes()
+
     def stream_reset(self, stream_id):
         check(load().ga_stream_reset(self._h, stream_id))
 

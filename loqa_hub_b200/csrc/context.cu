@@ -8,6 +8,7 @@
 // the boundary and CUDA failures.  There is no CPU fallback anywhere in this file.
 #include <algorithm>
 #include <atomic>
+#include <cstddef>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -653,6 +654,42 @@ extern "C" int ga_device_arena(ga_ctx *ctx, void **d_arena)
     if (!ctx || !d_arena) { set_error("ga_device_arena: NULL argument"); return GA_ERR_ARG; }
     if (!ctx->d_arena) { set_error("ga_device_arena: context does not materialise samples"); return GA_ERR_STATE; }
     *d_arena = ctx->d_arena;
+    return GA_OK;
+}
+
+extern "C" int ga_samples_digest(ga_ctx *ctx, uint32_t stream_id, uint8_t digest[32])
+{
+    if (!ctx || !digest || stream_id >= ctx->cfg.max_streams) { set_error("ga_samples_digest: bad argument"); return GA_ERR_ARG; }
+    if (!ctx->d_arena) { set_error("ga_samples_digest: context does not materialise samples"); return GA_ERR_STATE; }
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int rc = set_device(ctx);
+    if (rc) return rc;
+    const StreamState st = ctx->streams[stream_id];
+    if ((st.wake_n | st.speech_n) >> 30) { set_error("ga_samples_digest: stream too long for one chained hash"); return GA_ERR_ARG; }
+    // the two arena regions are hashed as two chained "messages" of one running SHA-256
+    struct Pack { ga_sha_state state; ga_desc desc[2]; uint32_t next[2]; uint32_t first[2]; uint8_t out[32]; };
+    static_assert(offsetof(Pack, desc) % 16 == 0, "descriptor alignment");
+    Pack h;
+    std::memset(&h, 0, sizeof h);
+    const uint64_t base = static_cast<uint64_t>(stream_id) * ctx->cfg.arena_samples * 4;
+    h.desc[0].in_off = base;                                   h.desc[0].nbytes = static_cast<uint32_t>(st.wake_n * 4);
+    h.desc[1].in_off = base + ctx->cfg.wake_samples_max * 4;   h.desc[1].nbytes = static_cast<uint32_t>(st.speech_n * 4);
+    h.desc[0].flags = GA_MSG_FIRST;                            // (re)starts the running hash
+    h.next[0] = 1; h.next[1] = 0xffffffffu; h.first[0] = 0;
+    uint8_t *d = nullptr;
+    GA_CUDA_TRY(cudaMalloc(reinterpret_cast<void **>(&d), sizeof(Pack)));
+    cudaStream_t s = ctx->aux;
+    cudaError_t e = cudaSuccess;
+    rc = join_inflight(ctx, s);
+    if (!rc) e = cudaMemcpyAsync(d, &h, sizeof h, cudaMemcpyHostToDevice, s);
+    Pack *dp = reinterpret_cast<Pack *>(d);
+    if (!rc && e == cudaSuccess) rc = ga_k_sha256_chain(ctx->d_arena, dp->desc, dp->first, dp->next, 1, &dp->state, s);
+    if (!rc && e == cudaSuccess) rc = ga_k_sha256_final(&dp->state, nullptr, 1, dp->out, nullptr, s);
+    if (!rc && e == cudaSuccess) e = cudaMemcpyAsync(digest, dp->out, 32, cudaMemcpyDeviceToHost, s);
+    if (!rc && e == cudaSuccess) e = cudaStreamSynchronize(s);
+    cudaFree(d);
+    if (rc) return rc;
+    if (e != cudaSuccess) { set_error("ga_samples_digest: %s", cudaGetErrorString(e)); return GA_ERR_CUDA; }
     return GA_OK;
 }
 

@@ -86,3 +86,20 @@ def test_utterance_only_context():
         res, _ = c.ingest([b"a" * 1000, b"b" * 24], [1, 1], [L.MSG_FIRST, 0])
         assert not res["digest"].any()
         assert c.utterance_digest(1) == (hashlib.sha256(b"a" * 1000 + b"b" * 24).digest(), 1024)
+
+
+def test_fingerprint_of_the_converted_samples(ctx):
+    """SURVEY §8c secondary mode: SHA-256 over the little-endian f32 bytes of WakeWordSignal ++
+    SpeechAudio (the serialisation of stt_client.go:390-395), hashed on the device."""
+    pcm = synth.relay_view(9, 2, 7000)
+    chunks = [pcm[i:i + 320].tobytes() for i in range(0, 7000, 320)]          # the last chunk is short
+    fl = np.zeros(len(chunks), np.uint32)
+    fl[:15] |= L.MSG_WAKE; fl[0] |= L.MSG_FIRST
+    ctx.ingest(chunks, np.full(len(chunks), 33, np.uint32), fl)
+    samples = ctx.fetch_samples(33)
+    assert samples.size == 7000
+    assert ctx.samples_digest(33) == hashlib.sha256(samples.astype("<f4").tobytes()).digest()
+    want, _ = ora.bytes_to_float32(pcm.tobytes())
+    assert ctx.samples_digest(33) == ora.sha256(want.astype("<f4").tobytes())
+    ctx.stream_reset(33)
+    assert ctx.samples_digest(33) == hashlib.sha256(b"").digest()
