@@ -429,9 +429,11 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
         set_error("ga_submit: batch needs %llu frame records, capacity %llu", (unsigned long long)frames, (unsigned long long)ctx->frames_cap);
         err = GA_ERR_OVERFLOW;
     }
-    if (err) {                                  // undo messages i-1 .. 0
-        while (i-- > 0) {
-            const ga_msg &m = msgs[i];
+    // undo messages upto-1 .. 0: a submit that fails — here or while queueing the GPU work
+    // below — leaves every stream cursor as it found it
+    auto undo = [&](uint32_t upto) {
+        while (upto-- > 0) {
+            const ga_msg &m = msgs[upto];
             StreamState &st = streams[m.stream_id];
             uint64_t ns = m.nbytes >> 1;
             if (fmt48) {
@@ -444,6 +446,9 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
             ((m.flags & GA_MSG_WAKE) ? st.wake_n : st.speech_n) -= ns;
             if (m.flags & GA_MSG_FIRST) { st = resets.back().before; resets.pop_back(); }
         }
+    };
+    if (err) {
+        undo(i);
         return err;
     }
     if (scattered) {   // more than 16 disjoint ranges: one covering copy
@@ -455,6 +460,7 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
     }
 
     cudaStream_t s = slot->stream;
+    auto enqueue = [&]() -> int {
     for (int r = 0; r < n_runs; r++)
         GA_CUDA_TRY(cudaMemcpyAsync(ctx->d_ring + runs[r].lo, ctx->h_ring + runs[r].lo, runs[r].hi - runs[r].lo, cudaMemcpyHostToDevice, s));
     if (n) {
@@ -490,7 +496,9 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
         }
         if (utter) {
             // the running digests make consecutive tickets dependent: chain them like the 48 kHz carry
-            GA_CUDA_TRY(cudaMemcpyAsync(slot->d_link, slot->h_link, sizeof(uint32_t) * 2 * ctx->cfg.max_batch_msgs, cudaMemcpyHostToDevice, s));
+            GA_CUDA_TRY(cudaMemcpyAsync(slot->d_link, slot->h_link, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, s));
+            GA_CUDA_TRY(cudaMemcpyAsync(slot->d_link + ctx->cfg.max_batch_msgs, slot->h_link + ctx->cfg.max_batch_msgs,
+                                        sizeof(uint32_t) * n_chains, cudaMemcpyHostToDevice, s));
             if (ctx->prev_kdone && !fmt48) GA_CUDA_TRY(cudaStreamWaitEvent(s, ctx->prev_kdone, 0));
             rc = ga_k_sha256_chain(ctx->d_ring, slot->d_desc, slot->d_link + ctx->cfg.max_batch_msgs, slot->d_link, n_chains, ctx->d_sha, s);
             if (rc) return rc;
@@ -504,6 +512,13 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
             GA_CUDA_TRY(cudaMemcpyAsync(slot->h_frames, slot->d_frames, sizeof(ga_frame) * frames, cudaMemcpyDeviceToHost, s));
     }
     GA_CUDA_TRY(cudaEventRecord(slot->done, s));
+    return GA_OK;
+    };
+    rc = enqueue();
+    if (rc) {
+        undo(n);
+        return rc;
+    }
     slot->busy = true;
     slot->ticket = ctx->next_ticket++;
     slot->n_msgs = n;

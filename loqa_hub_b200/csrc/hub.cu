@@ -212,13 +212,16 @@ extern "C" int ga_hub_on_chunk(ga_hub *h, const char *relay_id, const uint8_t *a
 extern "C" int ga_hub_flush(ga_hub *h, uint32_t *n_msgs)
 {
     if (!h) { set_error("ga_hub_flush: NULL hub"); return GA_ERR_ARG; }
-    std::lock_guard<std::mutex> lk(h->mu);
-    if (n_msgs) *n_msgs = static_cast<uint32_t>(h->pending.size());
-    if (h->pending.empty()) return GA_OK;
+    std::vector<ga_msg> batch;
+    {
+        std::lock_guard<std::mutex> lk(h->mu);   // only to take the queue: chunks keep arriving while the GPU works
+        batch.swap(h->pending);
+    }
+    if (n_msgs) *n_msgs = static_cast<uint32_t>(batch.size());
+    if (batch.empty()) return GA_OK;
     uint64_t ticket = 0;
-    int rc = ga_submit(h->ctx, h->pending.data(), static_cast<uint32_t>(h->pending.size()), &ticket);
+    int rc = ga_submit(h->ctx, batch.data(), static_cast<uint32_t>(batch.size()), &ticket);
     if (rc) return rc;
-    h->pending.clear();
     return ga_wait_view(h->ctx, ticket, nullptr, nullptr, nullptr, nullptr);
 }
 
