@@ -391,7 +391,11 @@ def main():
         threads = cpu_threads(args)
         host_pcm = pcm.cpu().numpy().view(np.uint8)
         v, reps, tt, ssl = run_cpu(host_pcm, w, S, threads, min_core_seconds=20.0, max_seconds=20.0)
-        cpu = {"value": v, "unit": "audio-s/s", "cores": threads, "kind": "port",
+        # one thread = one reference goroutine working alone (SURVEY.md §8d shape 1), on 1/8 of the streams
+        s1 = max(w["group_size"], S // 8 // w["group_size"] * w["group_size"])
+        pcm1 = np.ascontiguousarray(host_pcm.reshape(M, S, ms * 2)[:, :s1, :])
+        v1, _, _, _ = run_cpu(pcm1.reshape(-1), w, s1, 1, min_core_seconds=0.0, max_seconds=0.0)
+        cpu = {"value": v, "unit": "audio-s/s", "cores": threads, "kind": "port", "value_single_thread": v1,
                "sample": "%d x the full batch (%d streams x %d msgs x %d B) in %.2f s, OpenSSL SHA-256=%s, "
                          "no per-chunk logging" % (reps, S, M, ms * 2, tt, bool(ssl))}
 

@@ -221,7 +221,12 @@ extern "C" int ga_hub_flush(ga_hub *h, uint32_t *n_msgs)
     if (batch.empty()) return GA_OK;
     uint64_t ticket = 0;
     int rc = ga_submit(h->ctx, batch.data(), static_cast<uint32_t>(batch.size()), &ticket);
-    if (rc) return rc;
+    if (rc) {                                    // nothing was queued: the chunks stay pending, in order
+        std::lock_guard<std::mutex> lk(h->mu);
+        batch.insert(batch.end(), h->pending.begin(), h->pending.end());
+        h->pending.swap(batch);
+        return rc;
+    }
     return ga_wait_view(h->ctx, ticket, nullptr, nullptr, nullptr, nullptr);
 }
 
