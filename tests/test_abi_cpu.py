@@ -30,6 +30,25 @@ def test_library_loads_and_exports_every_declared_symbol():
     assert lib.ga_abi_version() == 1
 
 
+def test_header_is_plain_c_and_links_from_c(tmp_path):
+    """include/gpuaudio.h must be consumable by cgo, i.e. by a C compiler: compile it as strict C99
+    and link a C program that takes the address of every declared entry point against the .so."""
+    import subprocess
+    header = open(os.path.join(ROOT, "include", "gpuaudio.h")).read()
+    names = sorted(set(re.findall(r"\b(ga_[a-z0-9_]+)\s*\(", re.sub(r"/\*.*?\*/", "", header, flags=re.S))))
+    src = tmp_path / "abi.c"
+    src.write_text('#include "gpuaudio.h"\n#include <stdio.h>\nint main(void) {\n  void *p[] = {' +
+                   ", ".join("(void *)%s" % n for n in names) +
+                   '};\n  printf("%d %d\\n", (int)(sizeof p / sizeof p[0]), ga_abi_version());\n  return 0;\n}\n')
+    exe = tmp_path / "abi"
+    subprocess.check_call(["gcc", "-std=c99", "-pedantic", "-Wall", "-Wextra", "-Werror", "-Wno-pedantic",
+                           "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe),
+                           "-L", os.path.join(ROOT, "loqa_hub_b200"), "-lgpuaudio",
+                           "-Wl,-rpath," + os.path.join(ROOT, "loqa_hub_b200")])
+    out = subprocess.check_output([str(exe)]).decode().split()
+    assert int(out[0]) == len(names) == len(_lib.SYMBOLS) and int(out[1]) == 1
+
+
 def test_no_device_means_a_loud_error_not_a_fallback():
     if api.device_count() > 0:
         pytest.skip("a CUDA device is present")

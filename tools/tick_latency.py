@@ -16,11 +16,13 @@ from loqa_hub_b200 import api, synth  # noqa: E402
 ap = argparse.ArgumentParser()
 ap.add_argument("--streams", type=int, default=8192)
 ap.add_argument("--ticks", type=int, default=250)
+ap.add_argument("--utterance", action="store_true", help="also keep the per-utterance running SHA-256 (GA_DO_UTTERANCE)")
 args = ap.parse_args()
 S, ms, wake, group = args.streams, 320, 15, 8
 pcm = api.synth_batch_host(synth.SEED, 0, S, group, args.ticks, ms, n_threads=8).reshape(args.ticks, S * ms)
 ctx = api.Context(device=0, max_streams=S, max_batch_msgs=S, max_inflight=2, ring_bytes=S * ms * 2 * 8,
-                  arena_samples=args.ticks * ms, wake_samples_max=wake * ms, mode=L.DO_ALL)
+                  arena_samples=args.ticks * ms, wake_samples_max=wake * ms,
+                  mode=L.DO_ALL | (L.DO_UTTERANCE if args.utterance else 0))
 msgs = np.zeros(S, dtype=L.MSG_DTYPE)
 msgs["nbytes"] = ms * 2
 msgs["stream_id"] = np.arange(S)
@@ -42,7 +44,11 @@ for t in range(args.ticks):
         arb = time.perf_counter() - t0
         assert (winner == seg[:-1]).all()
 lat = np.array(lat[5:]) * 1e3
-print(json.dumps({"streams": S, "ticks": args.ticks, "tick_latency_ms": {"median": float(np.median(lat)),
+if args.utterance:
+    import hashlib
+    whole = pcm.reshape(args.ticks, S, ms)[:, 5, :].tobytes()
+    assert ctx.utterance_digest(5) == (hashlib.sha256(whole).digest(), len(whole))
+print(json.dumps({"streams": S, "ticks": args.ticks, "utterance_digest": bool(args.utterance), "tick_latency_ms": {"median": float(np.median(lat)),
       "p99": float(np.percentile(lat, 99)), "max": float(lat.max())},
       "arbitration_ms_all_windows": arb * 1e3, "windows": S // group,
       "real_time_budget_ms": 20.0, "h2d_bytes_per_tick": S * ms * 2 + S * 32, "d2h_bytes_per_tick": S * 64}))
