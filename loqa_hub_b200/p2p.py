@@ -53,7 +53,7 @@ def build_tables(plan, bases, region):
 class Exchange:
     """Device tables + argument block for one rank; .launch(stream) runs one step."""
 
-    def __init__(self, plan, region, bases, dev_arrays, to_device, timeout_cycles=4_000_000_000):
+    def __init__(self, plan, region, bases, dev_arrays, to_device, timeout_cycles=30_000_000_000):
         """dev_arrays: dict of device addresses {samples, wake_off, wake_n, status_in, seg, scores, winner,
         status_out}; to_device(np_array) -> object with .data_ptr() kept alive by the caller."""
         guest_dst, notify, wait, route_dst = build_tables(plan, bases, region)
