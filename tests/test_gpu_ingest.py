@@ -286,7 +286,7 @@ def test_cfg3_collision_groups_winners_match_cpu_baseline(ctx):
     assert ((s2[:, -1] - s2[:, -2]) / s2[:, -1] > 1e-3).all()
 
 
-@pytest.mark.parametrize("msg_bytes", [640, 128, 64, 16, 641 + 15, 3840, 1000 - 1000 % 16])
+@pytest.mark.parametrize("msg_bytes", [640, 128, 64, 16, 656, 3840, 992, 641, 3, 130])
 def test_uniform_batches_through_the_tensor_map_path(msg_bytes):
     """Equal-sized chunks back to back in the ring are staged with one 2-D TMA copy per 32 messages
     (ga_k_ingest_uniform, picked automatically by ga_submit); a context forced to per-message bulk
