@@ -183,3 +183,65 @@ def test_stream_audio_flow_many_groups_and_wav_for_winners(svc):
     assert not svc.on_chunk("later", pcm([100] * 320), True, False, 10_000 * MS + 100 * MS + 1)   # :990-995
     svc.flush()
     assert svc.poll(10_200 * MS) == 1 and svc.window(w).winner_id == "late"
+
+
+def test_concurrent_relay_threads_and_a_batching_thread(svc):
+    """What grpc-go does to the hub: one goroutine per relay stream calling the per-chunk handler
+    concurrently (StreamAudio :926) while ONE batching thread flushes ticks and runs the window
+    timer.  8 threads x 4 relays, 4 collision groups of 8; ctypes releases the GIL during the C
+    calls, so the hub's locking is really exercised."""
+    import threading
+    import time
+    groups, per_group, n_msgs, wake, ms = 4, 8, 20, 4, 320
+    ids = {(g, r): "t%d-%d" % (g, r) for g in range(groups) for r in range(per_group)}
+    for (g, r), rid in ids.items():
+        svc.connect(rid, group=g)
+    data = {k: synth.relay_view(300 + k[0], k[1], n_msgs * ms) for k in ids}
+    t0 = time.monotonic()
+    now_us = lambda: int((time.monotonic() - t0) * 1e6)
+    stop = threading.Event()
+    errors = []
+
+    def relay_thread(keys):
+        try:
+            for m in range(wake):                                  # wake word: all relays of a group within ~ms
+                for k in keys:
+                    assert svc.on_chunk(ids[k], data[k][m * ms:(m + 1) * ms].tobytes(), True, False, now_us())
+            time.sleep(0.15)                                       # the 100 ms windows close meanwhile
+            for m in range(wake, n_msgs):
+                for k in keys:
+                    if svc.is_relay_active(ids[k]):
+                        svc.on_chunk(ids[k], data[k][m * ms:(m + 1) * ms].tobytes(), False, m == n_msgs - 1, now_us())
+        except Exception as e:                                     # noqa: BLE001
+            errors.append(e)
+
+    def batcher():
+        try:
+            while not stop.is_set():
+                svc.flush()
+                svc.poll(now_us())
+                time.sleep(0.002)
+            svc.flush()
+        except Exception as e:                                     # noqa: BLE001
+            errors.append(e)
+
+    keys = sorted(ids)
+    threads = [threading.Thread(target=relay_thread, args=(keys[i::8],)) for i in range(8)]
+    bt = threading.Thread(target=batcher)
+    bt.start()
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    stop.set()
+    bt.join()
+    assert not errors, errors
+    for g in range(groups):
+        winner = ids[g, 0]
+        assert svc.relay(winner).status == RelayStatusWinner
+        assert sum(svc.relay(ids[g, r]).status == RelayStatusCancelled for r in range(per_group)) == per_group - 1
+        want = ora.signal_strength(ora.bytes_to_float32(data[g, 0][:wake * ms].tobytes())[0])[0]
+        assert svc.relay(winner).signal_strength == want
+        full, _ = ora.bytes_to_float32(data[g, 0].tobytes())
+        got = svc.ctx.fetch_samples(svc.relay(winner).slot)
+        assert np.array_equal(got.view(np.uint32), full.view(np.uint32))
