@@ -29,10 +29,12 @@ class RelayInfo:
 
 
 class AudioService:
-    def __init__(self, ctx: api.Context, max_streams, window_duration_us=0):
+    def __init__(self, ctx, max_streams, window_duration_us=0):
+        """ctx: an api.Context, or None for the bookkeeping-only hub the CPU tests use."""
         self.ctx = ctx
         self._h = C.c_void_p()
-        L.check(L.load().ga_hub_create(ctx._h, max_streams, window_duration_us, C.byref(self._h)))
+        L.check(L.load().ga_hub_create(ctx._h if ctx is not None else None, max_streams, window_duration_us,
+                                       C.byref(self._h)))
 
     def close(self):
         if self._h:

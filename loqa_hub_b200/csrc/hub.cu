@@ -72,7 +72,9 @@ static Relay *find_relay(ga_hub *h, const char *id)
 
 extern "C" int ga_hub_create(ga_ctx *ctx, uint32_t max_streams, uint64_t window_duration_us, ga_hub **out)
 {
-    if (!ctx || !out || max_streams == 0) { set_error("ga_hub_create: bad argument"); return GA_ERR_ARG; }
+    // ctx may be NULL: the registry and the window bookkeeping then work on their own (that is how
+    // the CPU-only tests run them); everything that needs samples reports GA_ERR_STATE
+    if (!out || max_streams == 0) { set_error("ga_hub_create: bad argument"); return GA_ERR_ARG; }
     ga_hub *h = new (std::nothrow) ga_hub;
     if (!h) { set_error("ga_hub_create: out of memory"); return GA_ERR_NOMEM; }
     h->ctx = ctx;
@@ -174,6 +176,7 @@ extern "C" int ga_hub_on_chunk(ga_hub *h, const char *relay_id, const uint8_t *a
     std::lock_guard<std::mutex> lk(h->mu);
     Relay *r = find_relay(h, relay_id);
     if (!r) { set_error("ga_hub_on_chunk: relay %s is not connected", relay_id); return GA_ERR_STATE; }
+    if (!h->ctx) { set_error("ga_hub_on_chunk: this hub has no GPU context"); return GA_ERR_STATE; }
     if (keep_stream) *keep_stream = 1;
     bool ingest = false;
     if (is_wake_word) {                                           // :962
@@ -212,6 +215,7 @@ extern "C" int ga_hub_on_chunk(ga_hub *h, const char *relay_id, const uint8_t *a
 extern "C" int ga_hub_flush(ga_hub *h, uint32_t *n_msgs)
 {
     if (!h) { set_error("ga_hub_flush: NULL hub"); return GA_ERR_ARG; }
+    if (!h->ctx) { set_error("ga_hub_flush: this hub has no GPU context"); return GA_ERR_STATE; }
     std::vector<ga_msg> batch;
     {
         std::lock_guard<std::mutex> lk(h->mu);   // only to take the queue: chunks keep arriving while the GPU works
@@ -233,6 +237,8 @@ extern "C" int ga_hub_flush(ga_hub *h, uint32_t *n_msgs)
 // performArbitration :505-587 for a set of windows at once.
 static int arbitrate_windows(ga_hub *h, const std::vector<uint64_t> &ids)
 {
+    if (ids.empty()) return GA_OK;
+    if (!h->ctx) { set_error("arbitration needs a GPU context"); return GA_ERR_STATE; }
     std::vector<uint32_t> seg(1, 0), sid, win_idx;
     std::vector<uint8_t> st_in, st_out;
     std::vector<double> scores;
@@ -379,7 +385,7 @@ extern "C" int ga_hub_cleanup_relay(ga_hub *h, const char *relay_id)
     const uint32_t slot = it->second.slot;
     h->relays.erase(it);
     h->free_slots.push_back(slot);
-    return ga_stream_reset(h->ctx, slot);
+    return h->ctx ? ga_stream_reset(h->ctx, slot) : GA_OK;
 }
 
 extern "C" int ga_hub_active_streams(ga_hub *h, uint32_t *n)
