@@ -129,3 +129,35 @@ def test_48k_boundary_rules(ctx48):
     assert ctx48.stream_info(2) == before                           # the failed submit left no trace
     res, _ = ctx48.ingest([b"\x01" * 400], [2], [L.MSG_FIRST])
     assert res["n_samples"][0] == 33
+
+
+def test_48k_context_with_utterance_digest_and_partial_fetches():
+    """All context options together on 48 kHz input: per-message digests of the received bytes, the
+    per-utterance running digest, frames, and ga_fetch_samples ranges that straddle the boundary
+    between the wake-word region and the speech region of the arena."""
+    import hashlib
+    import __graft_entry__ as entry
+    entry.build()
+    with api.Context(device=0, max_streams=8, max_batch_msgs=512, ring_bytes=8 << 20, arena_samples=20_000,
+                     wake_samples_max=4_000, mode=L.DO_ALL | L.DO_UTTERANCE, want_frames=True,
+                     input_format=L.FMT_STEREO48K) as c:
+        pcm = stereo48(11, 1, 960 * 20)
+        chunks = [pcm[i * 960:(i + 1) * 960].tobytes() for i in range(20)]
+        fl = np.zeros(20, np.uint32)
+        fl[:6] |= L.MSG_WAKE; fl[0] |= L.MSG_FIRST
+        r1, f1 = c.ingest(chunks[:9], np.full(9, 3, np.uint32), fl[:9])          # 6 wake + 3 speech chunks
+        r2, f2 = c.ingest(chunks[9:], np.full(11, 3, np.uint32), fl[9:])
+        res = np.concatenate([r1, r2])
+        parts = oracle_stream(chunks)
+        whole = np.concatenate(parts)
+        assert c.stream_info(3) == (20 * 320, 6 * 320)
+        assert np.array_equal(bits(c.fetch_samples(3)), bits(whole))
+        for first, n in ((0, 1), (1900, 40), (1919, 2), (1920, 5), (1000, 3000), (6399, 1), (6400, 0)):
+            assert np.array_equal(bits(c.fetch_samples(3, first, n)), bits(whole[first:first + n])), (first, n)
+        with pytest.raises(L.GpuAudioError):
+            c.fetch_samples(3, 6000, 401)
+        for i, data in enumerate(chunks):
+            assert res["digest"][i].tobytes() == hashlib.sha256(data).digest()
+        assert c.utterance_digest(3) == (hashlib.sha256(b"".join(chunks)).digest(), 20 * 3840)
+        assert len(f1) + len(f2) == 20
+        assert c.samples_digest(3) == hashlib.sha256(whole.astype("<f4").tobytes()).digest()
