@@ -68,6 +68,9 @@ def parse():
                     help="how message bytes reach shared memory: one 2-D TMA tensor copy per 32 messages "
                          "(uniform batches) or one bulk copy per message")
     ap.add_argument("--ticks-per-submit", type=int, default=10)
+    ap.add_argument("--submit", default="ticks", choices=["ticks", "msgs"],
+                    help="e2e leg: ga_submit_ticks (descriptors built on the GPU, 1 B per message over PCIe) "
+                         "or ga_submit with one 32-byte descriptor per message")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-threads", type=int, default=0)
@@ -484,7 +487,11 @@ def run_e2e(args, w, plan, pcm, arbitration, d_winner, world, rank, local_rank, 
 
     def wait(t):       # zero-copy: the result records stay in the C-owned pinned buffer
         L.check(lib.ga_wait_view(ctx._h, t, C.byref(res_p), None, C.byref(res_n), None))
-    h2d = ring_bytes + sub_msgs * n_sub * 32
+    ticks = args.submit == "ticks"
+    ids = np.arange(S, dtype=np.uint32)
+    tick_flags = [np.ascontiguousarray(mm["flags"].astype(np.uint8)) for mm in msgs]
+    # per-message descriptors (32 B each) or, for ga_submit_ticks, 1 flag byte per message + 12 B per stream
+    h2d = ring_bytes + (n_sub * (sub_msgs + 12 * S) if ticks else sub_msgs * n_sub * 32)
     d2h = sub_msgs * n_sub * 64 + plan.n_windows * 4
 
     def one_step(fill):
@@ -493,10 +500,13 @@ def run_e2e(args, w, plan, pcm, arbitration, d_winner, world, rank, local_rank, 
             view, off = ctx.reserve(sub_bytes)
             if fill:                                    # first pass only: the relays' bytes land in the ring
                 view[:sub_bytes] = host_pcm[j * sub_bytes:(j + 1) * sub_bytes]
-            mm = msgs[j]
-            mm["ring_offset"] = rel + np.uint64(off)
             t = C.c_uint64()
-            L.check(lib.ga_submit(ctx._h, L.ptr(mm), sub_msgs, C.byref(t)))
+            if ticks:
+                L.check(lib.ga_submit_ticks(ctx._h, off, tps, S, ms * 2, L.ptr(ids), L.ptr(tick_flags[j]), C.byref(t)))
+            else:
+                mm = msgs[j]
+                mm["ring_offset"] = rel + np.uint64(off)
+                L.check(lib.ga_submit(ctx._h, L.ptr(mm), sub_msgs, C.byref(t)))
             tickets.append(t.value)
             if len(tickets) == 4:
                 wait(tickets.pop(0))
@@ -536,8 +546,9 @@ def run_e2e(args, w, plan, pcm, arbitration, d_winner, world, rank, local_rank, 
     return {"value": audio_s * args.steps / dt, "unit": "audio-s/s", "h2d_bytes_per_step": int(h2d),
             "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * dt / args.steps,
             "h2d_gbs_per_gpu": h2d * args.steps / dt / 1e9,
-            "note": "host clock around ga_submit/ga_wait/arbitration, %d submits of %d msgs per step, "
-                    "4 tickets in flight" % (n_sub, sub_msgs)}
+            "submit": "ga_submit_ticks" if ticks else "ga_submit",
+            "note": "host clock around %s/ga_wait/arbitration, %d submits of %d msgs per step, "
+                    "4 tickets in flight" % ("ga_submit_ticks" if ticks else "ga_submit", n_sub, sub_msgs)}
 
 
 if __name__ == "__main__":

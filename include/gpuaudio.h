@@ -339,8 +339,27 @@ typedef struct ga_msg {
 
 /* One batch tick: H2D of the ring range + descriptors, the fused ingest launch, D2H of
  * the result records — all asynchronous.  Messages of one stream must appear in arrival
- * order.  Returns a ticket.  Called by the single batching goroutine. */
+ * order.  Returns a ticket.  Called by the single batching goroutine.
+ * A GA_MSG_FIRST message restarts its stream's sample buffers from empty (a new RelayStream,
+ * audio_service.go:945-958).  Contexts that convert refuse (GA_ERR_ARG) a restart that follows
+ * chunks of the same stream inside ONE batch — all messages of a batch are processed at once and
+ * both utterances would be written to the same arena space; send it with the next batch
+ * (ga_hub_flush splits its queue there).  Across batches the library orders the two itself. */
 int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *ticket);
+
+/* The same batch in its regular steady-state shape, described by a handful of numbers instead
+ * of one ga_msg per chunk: n_ticks chunk periods of n_streams relays, every relay sending one
+ * chunk of chunk_bytes per period (the StreamAudio loop, audio_service.go:939-1005, seen across
+ * all connected relays).  Message m = t * n_streams + j (t-th period, j-th relay) belongs to
+ * stream stream_ids[j], lies at ring_offset + m * round_up(chunk_bytes, 16) (one contiguous
+ * reservation) and carries flags[m] (GA_MSG_*, low 8 bits; NULL = none).  stream_ids must be
+ * distinct.  The per-message descriptors are built on the GPU from the per-stream cursors, so
+ * the host sends 1 byte per message and 12 per stream instead of 32 per message.  Results come
+ * back exactly as from ga_submit of the same n_ticks * n_streams messages.  Mono 16 kHz
+ * contexts without GA_DO_UTTERANCE only (GA_ERR_STATE otherwise). */
+int ga_submit_ticks(ga_ctx *ctx, uint64_t ring_offset, uint32_t n_ticks, uint32_t n_streams,
+                    uint32_t chunk_bytes, const uint32_t *stream_ids, const uint8_t *flags,
+                    uint64_t *ticket);
 
 /* Block until the ticket's results are on the host, then copy them out (results[n],
  * frames[] if the context wants frames — sized by ga_ticket_frames) and release the
@@ -412,7 +431,8 @@ int  ga_hub_join_window(ga_hub *hub, const char *relay_id, uint64_t now_us, int 
  * end of speech :1018-1021). */
 int  ga_hub_on_chunk(ga_hub *hub, const char *relay_id, const uint8_t *audio, uint32_t nbytes,
                      int is_wake_word, int is_end_of_speech, uint64_t now_us, int *keep_stream);
-/* Batch tick: one ga_submit + wait for everything queued since the last flush. */
+/* Batch tick: one ga_submit + wait for everything queued since the last flush (one more per
+ * relay that restarted an utterance inside the tick; *n_msgs = messages taken off the queue). */
 int  ga_hub_flush(ga_hub *hub, uint32_t *n_msgs);
 /* performArbitration :505-587 for one window (idempotent, :508-511) … */
 int  ga_hub_perform_arbitration(ga_hub *hub, uint64_t window_id);

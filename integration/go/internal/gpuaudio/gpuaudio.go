@@ -68,6 +68,23 @@ func (x *Ctx) Submit(msgs []Msg) (uint64, error) {
 	return uint64(t), nil
 }
 
+// SubmitTicks is Submit for the steady state: ticks chunk periods of the same relays, every
+// relay one chunk of chunkBytes per period, laid out period-major in ONE reservation at a stride
+// of chunkBytes rounded up to 16.  One flag byte per chunk crosses PCIe instead of a 32-byte
+// descriptor; the descriptors are built on the GPU.  flags may be nil.
+func (x *Ctx) SubmitTicks(off uint64, ticks int, slots []uint32, chunkBytes int, flags []uint8) (uint64, error) {
+	var t C.uint64_t
+	var fp *C.uint8_t
+	if flags != nil {
+		fp = (*C.uint8_t)(&flags[0])
+	}
+	if rc := C.ga_submit_ticks(x.c, C.uint64_t(off), C.uint32_t(ticks), C.uint32_t(len(slots)),
+		C.uint32_t(chunkBytes), (*C.uint32_t)(&slots[0]), fp, &t); rc != 0 {
+		return 0, lastErr(rc)
+	}
+	return uint64(t), nil
+}
+
 // Wait returns a view of the C-owned pinned result records (valid for 4 more Submits).
 func (x *Ctx) Wait(ticket uint64) ([]Result, error) {
 	var r *C.ga_result

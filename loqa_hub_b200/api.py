@@ -180,6 +180,22 @@ class Context:
         self._pending[t.value] = m.size
         return t.value
 
+    def submit_ticks(self, ring_offset, n_ticks, stream_ids, chunk_bytes, flags=None):
+        """ga_submit_ticks: n_ticks periods x len(stream_ids) relays, message t*S+j at
+        ring_offset + (t*S+j)*round16(chunk_bytes); flags is a u8 array [n_ticks*S] or None."""
+        ids = np.ascontiguousarray(stream_ids, dtype=np.uint32)
+        n = int(n_ticks) * ids.size
+        fl = None
+        if flags is not None:
+            fl = np.ascontiguousarray(flags, dtype=np.uint8)
+            if fl.size != n:
+                raise ValueError("flags must hold n_ticks * n_streams bytes")
+        t = C.c_uint64()
+        check(load().ga_submit_ticks(self._h, int(ring_offset), int(n_ticks), ids.size, int(chunk_bytes),
+                                     ptr(ids), ptr(fl) if fl is not None else None, C.byref(t)))
+        self._pending[t.value] = n
+        return t.value
+
     def wait(self, ticket):
         n = self._pending.pop(ticket)
         nf = C.c_uint32()

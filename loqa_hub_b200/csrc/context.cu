@@ -51,6 +51,7 @@ struct StreamState {
     uint64_t wake_n = 0;     // samples in the wake-word region   (RelayStream.WakeWordSignal)
     uint64_t speech_n = 0;   // samples in the speech region      (RelayStream.SpeechAudio)
     uint64_t n_frames = 0;   // 48 kHz input only: stereo frames consumed since the stream start
+    uint64_t stamp = 0;      // ticket of the batch that last appended to the stream
 };
 
 struct Slot {
@@ -62,6 +63,7 @@ struct Slot {
     uint32_t *h_link = nullptr, *d_link = nullptr;     // GA_DO_UTTERANCE: next[n] then run_first[n]
     ga_result *h_res = nullptr, *d_res = nullptr;
     ga_frame *h_frames = nullptr, *d_frames = nullptr;
+    uint8_t *h_tick = nullptr, *d_tick = nullptr;      // ga_submit_ticks: ids | wake0 | speech0 | flags
     uint64_t ticket = 0;
     uint64_t release_to = 0;
     uint32_t n_msgs = 0, n_frames = 0;
@@ -78,12 +80,15 @@ struct ga_ctx {
     ga_sha_state *d_sha = nullptr;             // GA_DO_UTTERANCE: running digest per stream
     std::vector<uint64_t> batch_stamp;         // 48 kHz input: ticket that last touched a stream ...
     std::vector<uint32_t> batch_last;          // ... and the index of that stream's latest message in it
+    std::vector<uint64_t> tick_stamp;          // ga_submit_ticks: duplicate-stream check
     uint64_t frames_cap = 0;
     std::atomic<uint64_t> ring_head{0}, ring_tail{0};
     std::vector<ga::StreamState> streams;
     std::vector<ga::Slot> slots;
     uint64_t next_ticket = 1, oldest_ticket = 1;
     cudaEvent_t prev_kdone = nullptr;
+    uint64_t fence_ticket = 0;                 // tickets up to this one must finish before the next batch's kernels
+                                               // start: a restarted stream reuses arena space they may still write
     uint8_t *d_arb = nullptr;                  // grow-only device scratch of ga_arbitrate (no per-call cudaMalloc)
     size_t arb_bytes = 0;
     std::mutex mu;   // guards submit/wait/arbitrate bookkeeping (not the ring reserve path)
@@ -117,6 +122,8 @@ static void destroy(ga_ctx *c)
         if (s.d_res) cudaFree(s.d_res);
         if (s.h_frames) cudaFreeHost(s.h_frames);
         if (s.d_frames) cudaFree(s.d_frames);
+        if (s.h_tick) cudaFreeHost(s.h_tick);
+        if (s.d_tick) cudaFree(s.d_tick);
         if (s.stream) cudaStreamDestroy(s.stream);
     }
     if (c->aux) cudaStreamDestroy(c->aux);
@@ -128,6 +135,9 @@ static void destroy(ga_ctx *c)
     if (c->d_arb) cudaFree(c->d_arb);
     delete c;
 }
+
+// ga_submit_ticks side buffer: three u32 arrays of up to cap streams, then cap flag bytes
+static size_t tick_bytes(uint32_t cap) { return (static_cast<size_t>(cap) * 13u + 63u) & ~static_cast<size_t>(63); }
 
 #define GA_ALLOC_TRY(expr)                                                            \
     do {                                                                              \
@@ -251,6 +261,14 @@ extern "C" int ga_init(const ga_config *cfg, ga_ctx **out)
             GA_ALLOC_TRY(cudaHostAlloc(reinterpret_cast<void **>(&s.h_frames), sizeof(ga_frame) * c->frames_cap, cudaHostAllocDefault));
             GA_ALLOC_TRY(cudaMalloc(reinterpret_cast<void **>(&s.d_frames), sizeof(ga_frame) * c->frames_cap));
         }
+        if (!fmt48 && !utter) {
+            GA_ALLOC_TRY(cudaHostAlloc(reinterpret_cast<void **>(&s.h_tick), tick_bytes(cfg->max_batch_msgs), cudaHostAllocDefault));
+            GA_ALLOC_TRY(cudaMalloc(reinterpret_cast<void **>(&s.d_tick), tick_bytes(cfg->max_batch_msgs)));
+        }
+    }
+    if (!fmt48 && !utter) {
+        try { c->tick_stamp.assign(cfg->max_streams, 0); }
+        catch (...) { set_error("ga_init: out of host memory"); destroy(c); return GA_ERR_NOMEM; }
     }
     GA_ALLOC_TRY(cudaStreamCreateWithFlags(&c->aux, cudaStreamNonBlocking));
     *out = c;
@@ -286,6 +304,17 @@ extern "C" int ga_ring_reserve(ga_ctx *ctx, uint64_t nbytes, void **host_ptr, ui
 }
 
 // ---------------------------------------------------------------- submit / wait
+// Tickets run on their own CUDA streams.  When a batch restarts a stream (GA_MSG_FIRST, or after
+// ga_stream_reset) whose previous chunks belong to a ticket still in flight, that ticket's kernel
+// may still be writing the arena space the new utterance starts over in: order the two.
+static int fence_wait(ga_ctx *ctx, cudaStream_t s, uint64_t fence)
+{
+    if (fence < ctx->oldest_ticket) return GA_OK;
+    for (auto &o : ctx->slots)
+        if (o.busy && o.ticket <= fence) GA_CUDA_TRY(cudaStreamWaitEvent(s, o.done, 0));
+    return GA_OK;
+}
+
 extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *ticket)
 {
     if (!ctx || !ticket || (n && !msgs)) { set_error("ga_submit: NULL argument"); return GA_ERR_ARG; }
@@ -308,7 +337,7 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
     // submit leaves the context exactly as it was.
     struct Saved { StreamState before; };
     std::vector<Saved> resets;                 // only GA_MSG_FIRST messages need a saved state
-    uint64_t release_to = tail, frames = 0;
+    uint64_t release_to = tail, frames = 0, fence = ctx->fence_ticket;
     struct Run { uint64_t lo, hi; };
     Run runs[16];
     int n_runs = 0;
@@ -341,7 +370,20 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
         if (i == 0) { phys0 = phys; ustride = need; }
         else if (uniform) uniform = (m.nbytes == msgs[0].nbytes) && (phys == phys0 + i * ustride);
         StreamState &st = streams[m.stream_id];
-        if (m.flags & GA_MSG_FIRST) { resets.push_back({st}); st = StreamState(); }
+        if (m.flags & GA_MSG_FIRST) {
+            // a new utterance reuses the stream's arena from its start while the batch's kernel may
+            // still be writing the old utterance's chunks there: it has to wait for the next batch
+            if (convert && st.stamp == stamp) {
+                set_error("ga_submit: msg %u starts a new utterance on stream %u after chunks of the previous one "
+                          "in the same batch; submit it with the next batch", i, m.stream_id);
+                err = GA_ERR_ARG;
+                break;
+            }
+            if (st.stamp > fence) fence = st.stamp;
+            resets.push_back({st});
+            st = StreamState();
+        }
+        st.stamp = stamp;
         uint64_t ns = m.nbytes >> 1;
         if (fmt48) {
             // 48 kHz stereo: the message yields one output per input frame index 3M+2 it contains
@@ -443,11 +485,14 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
                 ns = (n1 >= 3 * mf + 3) ? (n1 - 3 * mf - 3) / 3 + 1 : 0;
             }
             if (fmt48 || utter) ctx->batch_stamp[m.stream_id] = 0;
+            st.stamp = 0;
             ((m.flags & GA_MSG_WAKE) ? st.wake_n : st.speech_n) -= ns;
             if (m.flags & GA_MSG_FIRST) { st = resets.back().before; resets.pop_back(); }
         }
     };
     if (err) {
+        if (i < n && msgs[i].stream_id < max_streams && streams[msgs[i].stream_id].stamp == stamp)
+            streams[msgs[i].stream_id].stamp = 0;      // the refused message itself (undo covers those before it)
         undo(i);
         return err;
     }
@@ -461,6 +506,8 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
 
     cudaStream_t s = slot->stream;
     auto enqueue = [&]() -> int {
+    rc = fence_wait(ctx, s, fence);
+    if (rc) return rc;
     for (int r = 0; r < n_runs; r++)
         GA_CUDA_TRY(cudaMemcpyAsync(ctx->d_ring + runs[r].lo, ctx->h_ring + runs[r].lo, runs[r].hi - runs[r].lo, cudaMemcpyHostToDevice, s));
     if (n) {
@@ -519,11 +566,184 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
         undo(n);
         return rc;
     }
+    ctx->fence_ticket = 0;
     slot->busy = true;
     slot->ticket = ctx->next_ticket++;
     slot->n_msgs = n;
     slot->n_frames = static_cast<uint32_t>(frames);
     slot->release_to = release_to;
+    *ticket = slot->ticket;
+    return GA_OK;
+}
+
+// ---------------------------------------------------------------- regular tick batches
+namespace ga {
+
+// Descriptor of message m = t * n_streams + j from the stream's cursors at the start of the batch
+// and the flags of its earlier periods in the batch — the bookkeeping ga_submit does on the host
+// (append to WakeWordSignal or SpeechAudio, audio_service.go:965 / :1002), replayed per message.
+__global__ void __launch_bounds__(256)
+tick_desc_kernel(const uint32_t *__restrict__ ids, const uint32_t *__restrict__ wake0,
+                 const uint32_t *__restrict__ speech0, const uint8_t *__restrict__ flags, uint32_t n,
+                 uint32_t n_streams, uint32_t chunk_bytes, uint32_t stride, uint64_t phys0, uint64_t arena,
+                 uint64_t wake_cap, uint32_t frames_per_msg, int convert, ga_desc *__restrict__ desc)
+{
+    const uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= n) return;
+    const uint32_t t = m / n_streams, j = m - t * n_streams, ns = chunk_bytes >> 1;
+    uint32_t w = wake0[j], s = speech0[j];
+    if (flags) {
+        for (uint32_t k = 0; k < t; k++) {
+            const uint32_t f = flags[static_cast<size_t>(k) * n_streams + j];
+            if (f & GA_MSG_FIRST) { w = 0; s = 0; }
+            if (f & GA_MSG_WAKE) w += ns; else s += ns;
+        }
+    } else {
+        s += t * ns;
+    }
+    const uint32_t f = flags ? flags[m] : 0u;
+    if (f & GA_MSG_FIRST) { w = 0; s = 0; }
+    const uint32_t id = ids[j];
+    ga_desc d;
+    d.in_off = phys0 + static_cast<uint64_t>(m) * stride;
+    d.out_off = convert ? static_cast<uint64_t>(id) * arena + ((f & GA_MSG_WAKE) ? w : wake_cap + s) : 0;
+    d.nbytes = chunk_bytes;
+    d.stream_id = id;
+    d.flags = f;
+    d.frame_off = m * frames_per_msg;
+    uint4 *o = reinterpret_cast<uint4 *>(desc + m);
+    const uint4 *v = reinterpret_cast<const uint4 *>(&d);
+    o[0] = v[0];
+    o[1] = v[1];
+}
+
+}  // namespace ga
+
+extern "C" int ga_submit_ticks(ga_ctx *ctx, uint64_t ring_offset, uint32_t n_ticks, uint32_t n_streams,
+                               uint32_t chunk_bytes, const uint32_t *stream_ids, const uint8_t *flags,
+                               uint64_t *ticket)
+{
+    if (!ctx || !ticket || !stream_ids) { set_error("ga_submit_ticks: NULL argument"); return GA_ERR_ARG; }
+    if (n_ticks == 0 || n_streams == 0) { set_error("ga_submit_ticks: empty batch"); return GA_ERR_ARG; }
+    const uint64_t n64 = static_cast<uint64_t>(n_ticks) * n_streams;
+    if (n64 > ctx->cfg.max_batch_msgs) {
+        set_error("ga_submit_ticks: %llu messages exceed max_batch_msgs %u", (unsigned long long)n64, ctx->cfg.max_batch_msgs);
+        return GA_ERR_OVERFLOW;
+    }
+    const uint32_t n = static_cast<uint32_t>(n64);
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (ctx->tick_stamp.empty()) {
+        set_error("ga_submit_ticks: only for mono 16 kHz contexts without GA_DO_UTTERANCE; use ga_submit");
+        return GA_ERR_STATE;
+    }
+    const uint64_t arena = ctx->cfg.arena_samples, wake_cap = ctx->cfg.wake_samples_max;
+    const bool convert = (ctx->cfg.mode & GA_DO_CONVERT) != 0;
+    if (convert && arena > 0xffffffffull) { set_error("ga_submit_ticks: arena_samples beyond 2^32; use ga_submit"); return GA_ERR_STATE; }
+    int rc = set_device(ctx);
+    if (rc) return rc;
+    Slot *slot = nullptr;
+    for (auto &s : ctx->slots) if (!s.busy) { slot = &s; break; }
+    if (!slot) { set_error("ga_submit_ticks: %u tickets already in flight", ctx->cfg.max_inflight); return GA_ERR_STATE; }
+
+    const uint64_t size = ctx->cfg.ring_bytes;
+    const uint64_t stride = (static_cast<uint64_t>(chunk_bytes) + 15u) & ~15ull;
+    const uint64_t span = stride * n, phys0 = ring_offset % size;
+    const uint64_t head = ctx->ring_head.load(std::memory_order_acquire);
+    const uint64_t tail = ctx->ring_tail.load(std::memory_order_acquire);
+    if ((ring_offset & 15u) || ring_offset < tail || ring_offset + span > head || phys0 + span > size) {
+        set_error("ga_submit_ticks: [%llu, +%llu) is not one live reservation", (unsigned long long)ring_offset, (unsigned long long)span);
+        return GA_ERR_ARG;
+    }
+    // side buffer, packed so that one copy moves it: ids | wake0 | speech0 (n_streams each) | flags (n)
+    uint32_t *h_ids = reinterpret_cast<uint32_t *>(slot->h_tick), *h_wake0 = h_ids + n_streams, *h_speech0 = h_wake0 + n_streams;
+    uint8_t *h_flags = reinterpret_cast<uint8_t *>(h_speech0 + n_streams);
+    const uint64_t ns = chunk_bytes >> 1, frames_per_msg = (ns + GA_FRAME_SAMPLES - 1) / GA_FRAME_SAMPLES;
+    const uint64_t frames = frames_per_msg * n;
+    if (ctx->frames_cap && frames > ctx->frames_cap) {
+        set_error("ga_submit_ticks: batch needs %llu frame records, capacity %llu", (unsigned long long)frames, (unsigned long long)ctx->frames_cap);
+        return GA_ERR_OVERFLOW;
+    }
+    // per stream: remember where its cursors start, then replay its n_ticks chunks
+    std::vector<StreamState> before;
+    try { before.resize(n_streams); } catch (...) { set_error("ga_submit_ticks: out of host memory"); return GA_ERR_NOMEM; }
+    const uint64_t stamp = ctx->next_ticket;
+    uint64_t fence = ctx->fence_ticket;
+    StreamState *streams = ctx->streams.data();
+    uint32_t j = 0;
+    int err = GA_OK;
+    for (; j < n_streams && !err; j++) {
+        const uint32_t id = stream_ids[j];
+        if (id >= ctx->cfg.max_streams) { set_error("ga_submit_ticks: stream_ids[%u] = %u out of range", j, id); err = GA_ERR_ARG; break; }
+        if (ctx->tick_stamp[id] == stamp) { set_error("ga_submit_ticks: stream %u listed twice", id); err = GA_ERR_ARG; break; }
+        ctx->tick_stamp[id] = stamp;
+        StreamState &st = streams[id];
+        before[j] = st;
+        h_ids[j] = id;
+        h_wake0[j] = static_cast<uint32_t>(st.wake_n);
+        h_speech0[j] = static_cast<uint32_t>(st.speech_n);
+        for (uint32_t t = 0; t < n_ticks; t++) {
+            const uint32_t f = flags ? flags[static_cast<size_t>(t) * n_streams + j] : 0u;
+            if (f & GA_MSG_FIRST) {
+                if (convert && t > 0) {       // same rule as ga_submit: the old utterance's chunks are still in flight
+                    set_error("ga_submit_ticks: period %u starts a new utterance on stream %u after chunks of the "
+                              "previous one in the same batch; submit it with the next batch", t, id);
+                    err = GA_ERR_ARG;
+                    break;
+                }
+                if (st.stamp > fence) fence = st.stamp;
+                st = StreamState();
+            }
+            const bool is_wake = (f & GA_MSG_WAKE) != 0;
+            uint64_t &cursor = is_wake ? st.wake_n : st.speech_n;
+            if (convert && cursor + ns > (is_wake ? wake_cap : arena - wake_cap)) {
+                set_error("ga_submit_ticks: period %u overflows stream %u's %s sample arena", t, id, is_wake ? "wake-word" : "speech");
+                err = GA_ERR_OVERFLOW;
+                break;
+            }
+            cursor += ns;
+        }
+        if (err) { st = before[j]; ctx->tick_stamp[id] = 0; }
+        else st.stamp = stamp;
+    }
+    auto undo = [&](uint32_t upto) {
+        while (upto-- > 0) { streams[stream_ids[upto]] = before[upto]; ctx->tick_stamp[stream_ids[upto]] = 0; }
+    };
+    if (err) { undo(j); return err; }
+    if (flags) memcpy(h_flags, flags, n);
+
+    cudaStream_t s = slot->stream;
+    auto enqueue = [&]() -> int {
+        int r = fence_wait(ctx, s, fence);
+        if (r) return r;
+        if (span) GA_CUDA_TRY(cudaMemcpyAsync(ctx->d_ring + phys0, ctx->h_ring + phys0, span, cudaMemcpyHostToDevice, s));
+        uint32_t *d_ids = reinterpret_cast<uint32_t *>(slot->d_tick), *d_wake0 = d_ids + n_streams, *d_speech0 = d_wake0 + n_streams;
+        uint8_t *d_flags = reinterpret_cast<uint8_t *>(d_speech0 + n_streams);
+        GA_CUDA_TRY(cudaMemcpyAsync(slot->d_tick, slot->h_tick, 12ull * n_streams + (flags ? n : 0), cudaMemcpyHostToDevice, s));
+        tick_desc_kernel<<<(n + 255) / 256, 256, 0, s>>>(d_ids, d_wake0, d_speech0, flags ? d_flags : nullptr, n, n_streams, chunk_bytes,
+                                                        static_cast<uint32_t>(stride), phys0, arena, wake_cap,
+                                                        static_cast<uint32_t>(frames_per_msg), convert ? 1 : 0, slot->d_desc);
+        GA_CHECK_LAUNCH("tick_desc_kernel");
+        if (chunk_bytes && ctx->cfg.staging != GA_STAGING_BULK)
+            r = ga_k_ingest_uniform(ctx->d_ring, slot->d_desc, n, phys0, chunk_bytes, stride, ctx->d_arena, slot->d_res,
+                                    ctx->frames_cap ? slot->d_frames : nullptr, ctx->cfg.mode & GA_DO_ALL, ctx->cfg.vad_threshold, s);
+        else
+            r = ga_k_ingest(ctx->d_ring, slot->d_desc, n, ctx->d_arena, slot->d_res,
+                            ctx->frames_cap ? slot->d_frames : nullptr, ctx->cfg.mode & GA_DO_ALL, ctx->cfg.vad_threshold, s);
+        if (r) return r;
+        GA_CUDA_TRY(cudaMemcpyAsync(slot->h_res, slot->d_res, sizeof(ga_result) * n, cudaMemcpyDeviceToHost, s));
+        if (ctx->frames_cap && frames)
+            GA_CUDA_TRY(cudaMemcpyAsync(slot->h_frames, slot->d_frames, sizeof(ga_frame) * frames, cudaMemcpyDeviceToHost, s));
+        GA_CUDA_TRY(cudaEventRecord(slot->done, s));
+        return GA_OK;
+    };
+    rc = enqueue();
+    if (rc) { undo(n_streams); return rc; }
+    ctx->fence_ticket = 0;
+    slot->busy = true;
+    slot->ticket = ctx->next_ticket++;
+    slot->n_msgs = n;
+    slot->n_frames = static_cast<uint32_t>(frames);
+    slot->release_to = ring_offset + span > tail ? ring_offset + span : tail;
     *ticket = slot->ticket;
     return GA_OK;
 }
@@ -622,6 +842,7 @@ extern "C" int ga_stream_reset(ga_ctx *ctx, uint32_t stream_id)
 {
     if (!ctx || stream_id >= ctx->cfg.max_streams) { set_error("ga_stream_reset: bad argument"); return GA_ERR_ARG; }
     std::lock_guard<std::mutex> lk(ctx->mu);
+    if (ctx->streams[stream_id].stamp > ctx->fence_ticket) ctx->fence_ticket = ctx->streams[stream_id].stamp;
     ctx->streams[stream_id] = StreamState();   // cleanupRelay, audio_service.go:916-923
     if (ctx->d_sha) {
         int rc = set_device(ctx);

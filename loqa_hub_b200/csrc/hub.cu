@@ -19,6 +19,7 @@
 #include <mutex>
 #include <string>
 #include <unordered_map>
+#include <unordered_set>
 #include <vector>
 
 #include "common.cuh"
@@ -223,15 +224,35 @@ extern "C" int ga_hub_flush(ga_hub *h, uint32_t *n_msgs)
     }
     if (n_msgs) *n_msgs = static_cast<uint32_t>(batch.size());
     if (batch.empty()) return GA_OK;
-    uint64_t ticket = 0;
-    int rc = ga_submit(h->ctx, batch.data(), static_cast<uint32_t>(batch.size()), &ticket);
-    if (rc) {                                    // nothing was queued: the chunks stay pending, in order
-        std::lock_guard<std::mutex> lk(h->mu);
-        batch.insert(batch.end(), h->pending.begin(), h->pending.end());
-        h->pending.swap(batch);
-        return rc;
+    // A relay that finished an utterance and started the next one within one tick has chunks of
+    // both in the queue; ga_submit wants the restart in a later batch than the old chunks, so
+    // cut the queue there (rare: normally one submit).
+    std::vector<size_t> cuts;
+    bool any_first = false;
+    for (size_t k = 1; k < batch.size() && !any_first; k++) any_first = (batch[k].flags & GA_MSG_FIRST) != 0;
+    if (any_first) {
+        std::unordered_set<uint32_t> seen;
+        for (size_t k = 0; k < batch.size(); k++) {
+            if ((batch[k].flags & GA_MSG_FIRST) && seen.count(batch[k].stream_id)) { cuts.push_back(k); seen.clear(); }
+            seen.insert(batch[k].stream_id);
+        }
     }
-    return ga_wait_view(h->ctx, ticket, nullptr, nullptr, nullptr, nullptr);
+    cuts.push_back(batch.size());
+    size_t lo = 0;
+    for (size_t hi : cuts) {
+        uint64_t ticket = 0;
+        int rc = ga_submit(h->ctx, batch.data() + lo, static_cast<uint32_t>(hi - lo), &ticket);
+        if (rc) {                                // nothing of [lo, end) was queued: those chunks stay pending, in order
+            std::lock_guard<std::mutex> lk(h->mu);
+            h->pending.insert(h->pending.begin(), batch.begin() + lo, batch.end());
+            if (n_msgs) *n_msgs = static_cast<uint32_t>(lo);
+            return rc;
+        }
+        rc = ga_wait_view(h->ctx, ticket, nullptr, nullptr, nullptr, nullptr);
+        if (rc) return rc;
+        lo = hi;
+    }
+    return GA_OK;
 }
 
 // performArbitration :505-587 for a set of windows at once.

@@ -245,3 +245,26 @@ def test_concurrent_relay_threads_and_a_batching_thread(svc):
         full, _ = ora.bytes_to_float32(data[g, 0].tobytes())
         got = svc.ctx.fetch_samples(svc.relay(winner).slot)
         assert np.array_equal(got.view(np.uint32), full.view(np.uint32))
+
+
+def test_two_utterances_of_one_relay_inside_one_tick(svc):
+    """A relay whose next gRPC stream (= next utterance) starts before the batching tick has
+    flushed the previous one: both sit in the queue, the flush submits them as two batches, and
+    the stream ends up holding the second utterance only — as a fresh RelayStream would
+    (audio_service.go:945-958)."""
+    rid, other = "fast-relay", "steady-relay"
+    svc.connect(rid); svc.connect(other, group=1)
+    first = [pcm(np.full(320, 1000 + k)) for k in range(3)]
+    second = [pcm(np.full(320, -7000 - k)) for k in range(2)]
+    for k, c in enumerate(first):
+        assert svc.on_chunk(rid, c, True, False, k * MS)
+        assert svc.on_chunk(other, c, True, False, k * MS)
+    svc.connect(rid)                                     # new stream from the same relay, same tick
+    for k, c in enumerate(second):
+        assert svc.on_chunk(rid, c, True, False, (10 + k) * MS)
+    assert svc.flush() == 8
+    want = np.concatenate([ora.bytes_to_float32(c)[0] for c in second])
+    assert np.array_equal(svc.ctx.fetch_samples(svc.relay(rid).slot), want)
+    want_other = np.concatenate([ora.bytes_to_float32(c)[0] for c in first])
+    assert np.array_equal(svc.ctx.fetch_samples(svc.relay(other).slot), want_other)
+    assert svc.flush() == 0

@@ -231,8 +231,8 @@ def test_peak_of_negative_samples_in_either_half(ctx):
             for pos in range(n):
                 v = np.full(n, 5, dtype="<i2"); v[pos] = val
                 chunks.append(v.tobytes())
-            res, _ = ctx.ingest(chunks, np.arange(n, dtype=np.uint32) % 256,
-                                np.full(n, L.MSG_FIRST, np.uint32))
+            sid = np.arange(n, dtype=np.uint32) % 256
+            res, _ = ctx.ingest(chunks, sid, np.where(np.arange(n) < 256, L.MSG_FIRST, 0).astype(np.uint32))
             want = np.abs(np.float32(val) / np.float32(32767.0))
             assert (bits(res["peak"]) == bits(want)).all(), (val, n)
             assert (res["nonzero"] == n).all()
