@@ -462,6 +462,22 @@ int ga_bytes_to_float32(ga_ctx *ctx, const uint8_t *data, size_t len, float *out
 int ga_signal_strength(ga_ctx *ctx, const float *samples, size_t n, double *rms, ga_result *res);
 /* SHA-256 of an arbitrary host byte string (the fingerprint hook, events/voice_event.go:84-88). */
 int ga_sha256(ga_ctx *ctx, const uint8_t *data, size_t len, uint8_t digest[32]);
+/* VoiceEvent.SetAudioMetadata(audioData []float32, sampleRate, isWakeWord) with the fingerprint
+ * restored (events/voice_event.go:84-88; field removed by storage/migrations/
+ * 001_remove_audio_hash.sql): *audio_duration = float64(n) / float64(sample_rate) as the hook
+ * computes it, and audio_hash = "sha256:" + lowercase hex (the documented wire format,
+ * API.md:170) of the SHA-256 of the samples' little-endian IEEE-754 bytes, hashed on the GPU.
+ * zero_persistence != 0 (PrivacyConfig.ZeroPersistence, config/config.go:102-103) computes no
+ * fingerprint and returns audio_hash = "".  audio_hash holds GA_AUDIO_HASH_LEN bytes. */
+#define GA_AUDIO_HASH_LEN 72u   /* 7 + 64 + NUL */
+int ga_set_audio_metadata(ga_ctx *ctx, const float *audio_data, size_t n, int sample_rate,
+                          int zero_persistence, double *audio_duration, char *audio_hash);
+/* The same for a stream whose samples are already in HBM (ga_samples_digest) — what the hub
+ * calls for an arbitration winner after processWinningRelayAudio (audio_service.go:592-594). */
+int ga_stream_audio_metadata(ga_ctx *ctx, uint32_t stream_id, int sample_rate, int zero_persistence,
+                             double *audio_duration, char *audio_hash);
+/* "sha256:<hex>" of a 32-byte digest; pure host code. */
+void ga_format_audio_hash(const uint8_t digest[32], char *audio_hash);
 
 /* ===================================================================== utilities */
 

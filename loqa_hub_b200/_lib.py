@@ -82,6 +82,9 @@ SYMBOLS = {
     "ga_last_error": (C.c_char_p, []),
     "ga_ring_reserve": (_i32, [_vp, _u64, C.POINTER(_vp), C.POINTER(_u64)]),
     "ga_submit": (_i32, [_vp, _vp, _u32, C.POINTER(_u64)]),
+    "ga_set_audio_metadata": (_i32, [_vp, _vp, C.c_size_t, _i32, _i32, C.POINTER(C.c_double), C.c_char_p]),
+    "ga_stream_audio_metadata": (_i32, [_vp, _u32, _i32, _i32, C.POINTER(C.c_double), C.c_char_p]),
+    "ga_format_audio_hash": (None, [_vp, C.c_char_p]),
     "ga_submit_ticks": (_i32, [_vp, _u64, _u32, _u32, _u32, _vp, _vp, C.POINTER(_u64)]),
     "ga_wait": (_i32, [_vp, _u64, _vp, _vp]),
     "ga_wait_view": (_i32, [_vp, _u64, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_u32), C.POINTER(_u32)]),

@@ -1087,6 +1087,52 @@ extern "C" int ga_sha256(ga_ctx *ctx, const uint8_t *data, size_t len, uint8_t d
     return GA_OK;
 }
 
+// ---------------------------------------------------------------- voice-event hook
+extern "C" void ga_format_audio_hash(const uint8_t digest[32], char *audio_hash)
+{
+    static const char hex[] = "0123456789abcdef";
+    std::memcpy(audio_hash, "sha256:", 7);
+    for (int i = 0; i < 32; i++) {
+        audio_hash[7 + 2 * i] = hex[digest[i] >> 4];
+        audio_hash[8 + 2 * i] = hex[digest[i] & 15];
+    }
+    audio_hash[71] = 0;
+}
+
+// events/voice_event.go:84-88: float64(len(audioData)) / float64(sampleRate), Go semantics (a zero
+// rate gives +Inf / NaN, never an error); the fingerprint is over the samples as the hub
+// serialises them (stt_client.go:390-395).
+extern "C" int ga_set_audio_metadata(ga_ctx *ctx, const float *audio_data, size_t n, int sample_rate,
+                                     int zero_persistence, double *audio_duration, char *audio_hash)
+{
+    if (!ctx || (n && !audio_data) || !audio_duration || !audio_hash) { set_error("ga_set_audio_metadata: NULL argument"); return GA_ERR_ARG; }
+    *audio_duration = static_cast<double>(n) / static_cast<double>(sample_rate);
+    audio_hash[0] = 0;
+    if (zero_persistence) return GA_OK;
+    uint8_t digest[32];
+    int rc = ga_sha256(ctx, reinterpret_cast<const uint8_t *>(audio_data), n * sizeof(float), digest);
+    if (rc) return rc;
+    ga_format_audio_hash(digest, audio_hash);
+    return GA_OK;
+}
+
+extern "C" int ga_stream_audio_metadata(ga_ctx *ctx, uint32_t stream_id, int sample_rate, int zero_persistence,
+                                        double *audio_duration, char *audio_hash)
+{
+    if (!ctx || !audio_duration || !audio_hash) { set_error("ga_stream_audio_metadata: NULL argument"); return GA_ERR_ARG; }
+    uint64_t n = 0;
+    int rc = ga_stream_info(ctx, stream_id, &n, nullptr);
+    if (rc) return rc;
+    *audio_duration = static_cast<double>(n) / static_cast<double>(sample_rate);
+    audio_hash[0] = 0;
+    if (zero_persistence) return GA_OK;
+    uint8_t digest[32];
+    rc = ga_samples_digest(ctx, stream_id, digest);
+    if (rc) return rc;
+    ga_format_audio_hash(digest, audio_hash);
+    return GA_OK;
+}
+
 extern "C" int ga_signal_strength(ga_ctx *ctx, const float *samples, size_t n, double *rms, ga_result *res)
 {
     if (!ctx || (n && !samples) || !rms) { set_error("ga_signal_strength: NULL argument"); return GA_ERR_ARG; }

@@ -83,3 +83,14 @@ def test_host_batch_layout_and_relay_gain_ordering():
     e = (b.astype(np.float64) ** 2).sum(axis=(0, 2)).reshape(2, 8)
     assert (np.diff(e, axis=1) < 0).all()
     assert (e[:, :-1] / e[:, 1:] > 1.05).all()
+
+
+def test_audio_hash_wire_format():
+    """"sha256:" + lowercase hex (API.md:170) — pure host code, needs no device."""
+    import hashlib
+    from loqa_hub_b200.voice_event import format_audio_hash
+    d = hashlib.sha256(b"abc").digest()
+    assert format_audio_hash(d) == "sha256:ba7816bf8f01cfea414140de5dae2223b00361a396177a9cb410ff61f20015ad"
+    assert format_audio_hash(bytes(range(224, 256))) == "sha256:" + bytes(range(224, 256)).hex()
+    with pytest.raises(ValueError):
+        format_audio_hash(b"short")
