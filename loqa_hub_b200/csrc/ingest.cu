@@ -146,7 +146,7 @@ struct Span {
 };
 
 template <int CH, int STAGES, uint32_t MODE, int COOP>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32, (MODE == 7u) ? 5 : 1)
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, (MODE == 7u) ? 5 : 0)
 ingest_kernel(const IngestParams p, const __grid_constant__ CUtensorMap tmap)
 {
     constexpr bool kTmap = (COOP & 4) != 0;                                       // 2-D TMA staging (uniform batches)
