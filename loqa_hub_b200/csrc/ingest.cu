@@ -73,7 +73,14 @@ struct IngestParams {
     uint32_t n_msgs;
     uint32_t n_tiles;
     uint32_t msg_bytes;   // uniform batches only
+    uint32_t one;         // 1 (opaque to the assembler)
 };
+#ifndef GA_SCHED_IMAD
+#define GA_SCHED_IMAD true
+#endif
+#ifndef GA_ROUND_IMAD
+#define GA_ROUND_IMAD false
+#endif
 
 // One 2-D box [32 rows x 128 bytes] of the slab -> shared memory (SASS UTMALDG).
 __device__ __forceinline__ void tma_load_box(void *smem_dst, const CUtensorMap *tmap, uint32_t col, uint32_t row,
@@ -96,12 +103,23 @@ __device__ __forceinline__ const uint8_t *row_addr(const uint8_t *sbase, uint32_
 
 // Two int16 samples -> two exact floats without the conversion (XU) pipe: bias each half
 // by 0x8000, splice it under the exponent of 2^23 and subtract 2^23 + 32768.
+// kXu: use the conversion pipe after all (I2F.S16 with a half-word selector, no integer
+// instruction) — right when the kernel is bound by the ALU pipe (SHA-256 modes).
+template <bool kXu>
 __device__ __forceinline__ void unpack2(uint32_t w, float &lo, float &hi)
 {
+    if (kXu) {
+        lo = static_cast<float>(static_cast<short>(w & 0xffffu));
+        hi = static_cast<float>(static_cast<short>(w >> 16));
+        return;
+    }
     const uint32_t x = w ^ 0x80008000u;
     lo = __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7610)) - 8421376.0f;
     hi = __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7632)) - 8421376.0f;
 }
+#ifndef GA_XU_UNPACK
+#define GA_XU_UNPACK true
+#endif
 
 // Statistics of one span of samples in the reference's arithmetic.  `sum` is the strictly
 // sequential float64 chain; the order-independent pieces are kept packed: max/min of both
@@ -315,8 +333,8 @@ ingest_kernel(const IngestParams p, const __grid_constant__ CUtensorMap tmap)
 #pragma unroll
                             for (int j = 0; j < 16; j += 2) {
                                 float v0, v1, v2, v3;
-                                unpack2(w[j], v0, v1);
-                                unpack2(w[j + 1], v2, v3);
+                                unpack2<kSha && GA_XU_UNPACK>(w[j], v0, v1);
+                                unpack2<kSha && GA_XU_UNPACK>(w[j + 1], v2, v3);
                                 const float x0 = pcm_to_f32(v0), x1 = pcm_to_f32(v1);
                                 const float x2 = pcm_to_f32(v2), x3 = pcm_to_f32(v3);
                                 if (kCoop) {
@@ -351,7 +369,7 @@ ingest_kernel(const IngestParams p, const __grid_constant__ CUtensorMap tmap)
                             for (uint32_t k = 0; k < ns; k++) {
                                 const uint32_t h = *reinterpret_cast<const uint16_t *>(row_addr<kTmap, L::kRowStride>(sbase, lane, b * 64 + 2 * k));
                                 float v0, v1;
-                                unpack2(h, v0, v1);
+                                unpack2<false>(h, v0, v1);
                                 const float x0 = pcm_to_f32(v0);
                                 if (kCoop) orow[b * 32 + k] = x0;
                                 else if (kLaneStore) p.samples[out_off + (lo >> 1) + b * 32 + k] = x0;
@@ -384,7 +402,7 @@ ingest_kernel(const IngestParams p, const __grid_constant__ CUtensorMap tmap)
                             w[14] = static_cast<uint32_t>(bits >> 32);
                             w[15] = static_cast<uint32_t>(bits);
                         }
-                        sha256_compress(sha, w);
+                        sha256_compress<GA_SCHED_IMAD, GA_ROUND_IMAD>(sha, w, p.one);
                     }
                 }
                 if (kFeat && last && frm.n) emit_frame();
@@ -532,6 +550,7 @@ extern "C" int ga_k_ingest(const void *d_pcm, const ga_desc *d_desc, uint32_t n_
     p.n_msgs = n_msgs;
     p.n_tiles = (n_msgs + 31) / 32;
     p.msg_bytes = 0;
+    p.one = 1;
     CUtensorMap none;
     memset(&none, 0, sizeof none);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -583,6 +602,7 @@ extern "C" int ga_k_ingest_uniform(const void *d_pcm, const ga_desc *d_desc, uin
     p.n_msgs = n_msgs;
     p.n_tiles = (n_msgs + 31) / 32;
     p.msg_bytes = msg_bytes;
+    p.one = 1;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     switch (mode) {
         case 1: return launch_ingest<128, 2, 1, 5>(p, tmap, st);

@@ -21,10 +21,26 @@ struct Sha256State {
     }
 };
 
+// a + b issued as IMAD a*one+b: `one` is a kernel parameter equal to 1 that the assembler cannot
+// fold, so the addition runs on the FMA pipe instead of the ALU pipe
+__device__ __forceinline__ uint32_t add_fma_pipe(uint32_t a, uint32_t b, uint32_t one)
+{
+    uint32_t r;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(one), "r"(b));
+    return r;
+}
+
 #define GA_SHA_ROUND(a, b, c, d, e, f, g, h, k, w)                                   \
     {                                                                                \
-        uint32_t t1 = (h) + (rotr(e, 6) ^ rotr(e, 11) ^ rotr(e, 25)) +               \
-                      (((e) & (f)) ^ (~(e) & (g))) + (k) + (w);                      \
+        uint32_t t1;                                                                 \
+        if (kImadRound) {                                                            \
+            /* h + k + w does not depend on this round's e: two FMA-pipe additions */ \
+            const uint32_t hkw_ = add_fma_pipe(add_fma_pipe((w), (k), one), (h), one); \
+            t1 = hkw_ + (rotr(e, 6) ^ rotr(e, 11) ^ rotr(e, 25)) + (((e) & (f)) ^ (~(e) & (g))); \
+        } else {                                                                     \
+            t1 = (h) + (rotr(e, 6) ^ rotr(e, 11) ^ rotr(e, 25)) +                    \
+                 (((e) & (f)) ^ (~(e) & (g))) + (k) + (w);                           \
+        }                                                                            \
         uint32_t t2 = (rotr(a, 2) ^ rotr(a, 13) ^ rotr(a, 22)) +                     \
                       (((a) & (b)) ^ ((a) & (c)) ^ ((b) & (c)));                     \
         (d) += t1;                                                                   \
@@ -34,12 +50,20 @@ struct Sha256State {
 #define GA_SHA_SCHED(w, i)                                                           \
     {                                                                                \
         uint32_t x15 = w[((i) + 1) & 15], x2 = w[((i) + 14) & 15];                   \
-        w[(i) & 15] += (rotr(x15, 7) ^ rotr(x15, 18) ^ (x15 >> 3)) + w[((i) + 9) & 15] + \
-                       (rotr(x2, 17) ^ rotr(x2, 19) ^ (x2 >> 10));                   \
+        const uint32_t s0_ = rotr(x15, 7) ^ rotr(x15, 18) ^ (x15 >> 3);              \
+        const uint32_t s1_ = rotr(x2, 17) ^ rotr(x2, 19) ^ (x2 >> 10);               \
+        if (kImad) {                                                                 \
+            uint32_t t_ = add_fma_pipe(s0_, w[(i) & 15], one);                       \
+            t_ = add_fma_pipe(w[((i) + 9) & 15], t_, one);                           \
+            w[(i) & 15] = add_fma_pipe(s1_, t_, one);                                \
+        } else {                                                                     \
+            w[(i) & 15] += s0_ + w[((i) + 9) & 15] + s1_;                            \
+        }                                                                            \
     }
 
 // w[16] holds the block as big-endian words on entry and is clobbered.
-__device__ __forceinline__ void sha256_compress(Sha256State &s, uint32_t (&w)[16])
+template <bool kImad = false, bool kImadRound = false>
+__device__ __forceinline__ void sha256_compress(Sha256State &s, uint32_t (&w)[16], uint32_t one = 1u)
 {
     uint32_t a = s.h[0], b = s.h[1], c = s.h[2], d = s.h[3];
     uint32_t e = s.h[4], f = s.h[5], g = s.h[6], h = s.h[7];
