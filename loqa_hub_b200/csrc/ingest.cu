@@ -78,6 +78,9 @@ struct IngestParams {
 #ifndef GA_SCHED_IMAD
 #define GA_SCHED_IMAD true
 #endif
+#ifndef GA_SHA_ROLLED
+#define GA_SHA_ROLLED true
+#endif
 #ifndef GA_ROUND_IMAD
 #define GA_ROUND_IMAD false
 #endif
@@ -402,7 +405,9 @@ ingest_kernel(const IngestParams p, const __grid_constant__ CUtensorMap tmap)
                             w[14] = static_cast<uint32_t>(bits >> 32);
                             w[15] = static_cast<uint32_t>(bits);
                         }
-                        sha256_compress<GA_SCHED_IMAD, GA_ROUND_IMAD>(sha, w, p.one);
+                        // next to the conversion code the unrolled rounds overflow the 32 KB instruction
+                        // cache: fused instantiations run rounds 16..63 as a 3-pass loop
+                        sha256_compress<GA_SCHED_IMAD, GA_ROUND_IMAD, GA_SHA_ROLLED && (kFeat || kLaneStore || kCoop)>(sha, w, p.one);
                     }
                 }
                 if (kFeat && last && frm.n) emit_frame();
