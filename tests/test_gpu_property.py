@@ -1,0 +1,176 @@
+"""Property test of the context layer: ANY batch the boundary accepts — ragged lengths, shuffled
+streams, wake/speech flags, every mode and both staging paths — must come back bit-identical to the
+CPU oracle, record by record, frame by frame, and sample by sample in the stream arenas.
+Hypothesis draws the batches (derandomised, so the run is the same everywhere)."""
+import numpy as np
+import pytest
+from hypothesis import HealthCheck, given, settings
+from hypothesis import strategies as st
+
+from loqa_hub_b200 import _lib as L
+from loqa_hub_b200 import api
+from oracle import oracle as ora
+
+pytestmark = pytest.mark.gpu
+
+N_STREAMS = 12
+_ctx = {}
+
+
+def context(mode, staging, frames):
+    key = (mode, staging, frames)
+    if key not in _ctx:
+        import __graft_entry__ as entry
+        entry.build()
+        _ctx[key] = api.Context(device=0, max_streams=N_STREAMS, max_batch_msgs=256, max_inflight=2,
+                                ring_bytes=4 << 20, arena_samples=400_000, wake_samples_max=100_000,
+                                mode=mode, want_frames=frames, staging=staging)
+    return _ctx[key]
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _close_contexts():
+    yield
+    for c in _ctx.values():
+        c.close()
+    _ctx.clear()
+
+
+lengths = st.one_of(st.integers(0, 200), st.integers(630, 650), st.integers(1270, 1290),
+                    st.integers(0, 4000), st.sampled_from([55, 56, 63, 64, 65, 119, 120, 127, 128, 129, 640]))
+kinds = st.sampled_from(["random", "zeros", "max", "min", "alternating", "small"])
+
+
+def payload(kind, n, seed):
+    rng = np.random.default_rng(seed)
+    if kind == "random":
+        return rng.integers(0, 256, size=n, dtype=np.uint8).tobytes()
+    if kind == "zeros":
+        return bytes(n)
+    v = {"max": [32767], "min": [-32768], "alternating": [32767, -32768, 0], "small": [1, -1, 0, 0]}[kind]
+    return np.resize(np.asarray(v, dtype="<i2"), (n + 1) // 2).tobytes()[:n]
+
+
+batches = st.lists(st.tuples(lengths, kinds, st.integers(0, N_STREAMS - 1), st.booleans()), min_size=1, max_size=48)
+
+
+@settings(max_examples=200, deadline=None, derandomize=True,
+          suppress_health_check=[HealthCheck.too_slow, HealthCheck.data_too_large])
+@given(batch=batches, uniform_len=st.one_of(st.none(), st.sampled_from([2, 64, 640, 642, 1000])),
+       mode=st.sampled_from([L.DO_ALL, L.DO_CONVERT | L.DO_FEATURES, L.DO_SHA256, L.DO_SHA256 | L.DO_FEATURES,
+                             L.DO_CONVERT | L.DO_SHA256, L.DO_FEATURES, L.DO_CONVERT]),
+       staging=st.sampled_from([L.STAGING_AUTO, L.STAGING_BULK]), frames=st.booleans(), seed=st.integers(0, 2 ** 31))
+def test_any_accepted_batch_matches_the_oracle(batch, uniform_len, mode, staging, frames, seed):
+    c = context(mode, staging, frames)
+    chunks, sids, flags, seen = [], [], [], set()
+    for i, (n, kind, sid, wake) in enumerate(batch):
+        if uniform_len is not None:
+            n = uniform_len                       # equal sizes pushed back to back: the tensor-map path
+        chunks.append(payload(kind, n, seed + i))
+        sids.append(sid)
+        flags.append((L.MSG_WAKE if wake else 0) | (0 if sid in seen else L.MSG_FIRST))   # restart each stream once
+        seen.add(sid)
+    res, fr = c.ingest(chunks, sids, flags)
+    want_wake = {s: [] for s in seen}
+    want_speech = {s: [] for s in seen}
+    fpos = 0
+    for i, data in enumerate(chunks):
+        x, cs = ora.bytes_to_float32(data)
+        rms, ss = ora.signal_strength(x)
+        r = res[i]
+        if mode & L.DO_SHA256:
+            assert r["digest"].tobytes() == ora.sha256(data), (i, len(data))
+        else:
+            assert not r["digest"].any()
+        assert r["n_samples"] == x.size and (r["flags"] >> 8) == flags[i]
+        if mode & L.DO_FEATURES:
+            assert (r["sumsq"], r["rms"], r["nonzero"]) == (ss.sumsq, rms, ss.nonzero), (i, len(data))
+            assert np.float32(r["peak"]).view(np.uint32) == np.float32(cs.peak).view(np.uint32)
+            assert (r["flags"] & 1) == (1 if rms > 0.01 else 0)
+            if frames:
+                of = ora.frame_features(x, L.FRAME_SAMPLES, 0.01)
+                for a, b in zip(fr[fpos:fpos + len(of)], of):
+                    assert (a["sumsq"], a["rms"], a["n_samples"], a["nonzero"], a["vad"]) == \
+                           (b["sumsq"], b["rms"], b["n_samples"], b["nonzero"], b["vad"])
+        if frames:
+            fpos += (x.size + L.FRAME_SAMPLES - 1) // L.FRAME_SAMPLES
+        (want_wake if flags[i] & L.MSG_WAKE else want_speech)[sids[i]].append(x)
+    if frames:
+        assert fpos == len(fr)
+    for s in seen:
+        w = np.concatenate(want_wake[s]) if want_wake[s] else np.zeros(0, np.float32)
+        sp = np.concatenate(want_speech[s]) if want_speech[s] else np.zeros(0, np.float32)
+        assert c.stream_info(s) == (w.size + sp.size, w.size)
+        if mode & L.DO_CONVERT:
+            got = c.fetch_samples(s)
+            assert got.view(np.uint32).tobytes() == np.concatenate([w, sp]).view(np.uint32).tobytes(), s
+
+
+# ---------------------------------------------------------------- 48 kHz stereo + running digest
+chunk48 = st.one_of(st.integers(0, 40), st.integers(180, 200), st.just(3840), st.integers(0, 3840),
+                    st.sampled_from([4 * 46, 4 * 47, 4 * 48, 4 * 959 + 1, 3839]))
+
+
+@settings(max_examples=150, deadline=None, derandomize=True,
+          suppress_health_check=[HealthCheck.too_slow, HealthCheck.data_too_large])
+@given(plan=st.lists(st.tuples(st.integers(0, 3), chunk48, st.booleans()), min_size=1, max_size=40),
+       seed=st.integers(0, 2 ** 31))
+def test_48k_streams_any_chunking_any_batching(plan, seed):
+    """Four 48 kHz stereo streams cut into arbitrary chunks (partial frames, chunks shorter than the
+    filter history, empty ones) and arbitrary batches: samples, statistics and the running
+    per-utterance digest must not depend on where the cuts fall.  `new_batch` closes the current
+    batch; one is also closed where the boundary demands it (a chunk whose stream's previous
+    chunk in the batch is shorter than the 47-frame history)."""
+    import hashlib
+    key = ("48k",)
+    if key not in _ctx:
+        import __graft_entry__ as entry
+        entry.build()
+        _ctx[key] = api.Context(device=0, max_streams=4, max_batch_msgs=64, max_inflight=2, ring_bytes=2 << 20,
+                                arena_samples=60_000, wake_samples_max=20_000, mode=L.DO_ALL | L.DO_UTTERANCE,
+                                want_frames=True, input_format=L.FMT_STEREO48K)
+    c = _ctx[key]
+    rng = np.random.default_rng(seed)
+    oracle = [ora.Resampler() for _ in range(4)]
+    received = [b"" for _ in range(4)]
+    want = [[] for _ in range(4)]
+    started = [False] * 4
+    batch, last_len = [], {}
+
+    def flush():
+        if not batch:
+            return
+        res, fr = c.ingest([b[1] for b in batch], [b[0] for b in batch], [b[2] for b in batch])
+        fpos = 0
+        for r, (sid, data, _fl, y) in zip(res, batch):
+            rms, ss = ora.signal_strength(y)
+            assert r["digest"].tobytes() == hashlib.sha256(data).digest()
+            assert (r["n_samples"], r["nonzero"], r["sumsq"], r["rms"]) == (y.size, ss.nonzero, ss.sumsq, rms)
+            of = ora.frame_features(y, L.FRAME_SAMPLES, 0.01)
+            for a, b in zip(fr[fpos:fpos + len(of)], of):
+                assert (a["sumsq"], a["n_samples"], a["nonzero"]) == (b["sumsq"], b["n_samples"], b["nonzero"])
+            fpos += len(of)
+        assert fpos == len(fr)
+        batch.clear()
+        last_len.clear()
+
+    for sid, nbytes, new_batch in plan:
+        if new_batch or (sid in last_len and last_len[sid] < 47 * 4):
+            flush()
+        data = rng.integers(0, 256, size=nbytes, dtype=np.uint8).tobytes()
+        y = oracle[sid].process(data)
+        fl = 0 if started[sid] else L.MSG_FIRST
+        started[sid] = True
+        received[sid] += data
+        want[sid].append(y)
+        batch.append((sid, data, fl, y))
+        last_len[sid] = nbytes
+    flush()
+    for sid in range(4):
+        if not started[sid]:
+            continue
+        y = np.concatenate(want[sid])
+        assert c.stream_info(sid) == (y.size, 0)
+        assert c.fetch_samples(sid).view(np.uint32).tobytes() == y.view(np.uint32).tobytes()
+        digest, n = c.utterance_digest(sid)
+        assert (bytes(digest), n) == (hashlib.sha256(received[sid]).digest(), len(received[sid]))
