@@ -174,3 +174,50 @@ def test_48k_streams_any_chunking_any_batching(plan, seed):
         assert c.fetch_samples(sid).view(np.uint32).tobytes() == y.view(np.uint32).tobytes()
         digest, n = c.utterance_digest(sid)
         assert (bytes(digest), n) == (hashlib.sha256(received[sid]).digest(), len(received[sid]))
+
+
+# ---------------------------------------------------------------- arbitration
+member = st.tuples(st.integers(0, 2600), st.sampled_from(["random", "zeros", "max", "small", "quiet"]),
+                   st.sampled_from([L.RELAY_CONTENDING] * 4 + [L.RELAY_CONNECTED, L.RELAY_WINNER, L.RELAY_CANCELLED]))
+
+
+@settings(max_examples=120, deadline=None, derandomize=True,
+          suppress_health_check=[HealthCheck.too_slow, HealthCheck.data_too_large])
+@given(windows=st.lists(st.lists(member, min_size=0, max_size=9), min_size=1, max_size=7), seed=st.integers(0, 2 ** 31),
+       twin=st.booleans())
+def test_any_set_of_windows_arbitrates_like_the_reference(windows, seed, twin):
+    """performArbitration (audio_service.go:505-571) for arbitrary windows — empty ones, empty and
+    all-zero wake-word signals (first-member fallback), members that are not contending (skipped,
+    :522-524), exact ties (`twin`: two members hear identical audio; the first in join order keeps
+    the win because the comparison is a strict `>`)."""
+    c = context(L.DO_ALL, L.STAGING_AUTO, False)
+    rng = np.random.default_rng(seed)
+    sid, chunks, flags, sig, status, seg = 0, [], [], [], [], [0]
+    for w in windows:
+        w = w[:N_STREAMS - sid]                   # the context has N_STREAMS stream slots
+        for k, (n, kind, st_in) in enumerate(w):
+            if kind == "quiet":
+                data = rng.integers(-3, 4, size=n).astype("<i2").tobytes()
+            else:
+                data = payload(kind, 2 * n, seed + sid)
+            if twin and k == 1:
+                data = prev                        # same bytes as the window's first member
+            prev = data
+            chunks.append(data); flags.append(L.MSG_WAKE | L.MSG_FIRST)
+            sig.append(ora.bytes_to_float32(data)[0]); status.append(st_in)
+            sid += 1
+        seg.append(sid)
+    if sid:
+        c.ingest(chunks, list(range(sid)), flags)
+    winner, scores, st_out = c.arbitrate(np.array(seg, np.uint32), np.arange(sid, dtype=np.uint32),
+                                         np.array(status, np.uint8), np.full(sid, -1.0))
+    for k in range(len(seg) - 1):
+        lo, hi = seg[k], seg[k + 1]
+        w, sc, so = ora.arbitrate(sig[lo:hi], np.array(status[lo:hi], np.uint8))
+        assert int(winner[k]) == (lo + w if w >= 0 else 0xffffffff), (k, lo, hi)
+        for m in range(lo, hi):
+            if status[m] == L.RELAY_CONTENDING:
+                assert scores[m] == sc[m - lo]
+            else:
+                assert scores[m] == -1.0           # relay.SignalStrength untouched for skipped relays
+        assert list(st_out[lo:hi]) == list(so)
