@@ -16,6 +16,9 @@
  *   parity unpinned : ora_frame_features (20 ms framing), ora_resample_48k_stereo
  *              (÷3 polyphase), — new-spec pieces that have no reference code;
  *              this restatement IS their definition.
+ *              The decimator is additionally held, bit for bit, to an independent
+ *              exact-rational evaluation of the same definition
+ *              (oracle/numpy_mirror.py Resampler, tests/golden/path_golden.json).
  *   pinned by format : ora_float32_to_wav — restates internal/llm/stt_client.go:365-398.
  *
  * All citations are relative to /root/reference.
