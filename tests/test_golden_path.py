@@ -74,7 +74,43 @@ def test_oracle_wav_and_utterance(g):
         assert ora.sha256(acc).hex() == want
 
 
+def _frame_tuple(a):
+    return (int(a["n_samples"]), struct.pack("<d", a["sumsq"]).hex(), struct.pack("<d", a["rms"]).hex(),
+            int(a["nonzero"]), int(np.float32(a["peak"]).view(np.uint32)), int(a["vad"]))
+
+
+def _want_frames(m):
+    return [(f["n_samples"], f["sumsq_f64_hex"], f["rms_f64_hex"], f["nonzero"], f["peak_bits"], f["vad"])
+            for f in m["frames"]]
+
+
+def test_oracle_frame_features(g):
+    for m in g["frames"]:
+        x, _ = ora.bytes_to_float32(bytes.fromhex(m["pcm_hex"]))
+        got = ora.frame_features(x, 320, 0.01)
+        assert [_frame_tuple(a) for a in got] == _want_frames(m)
+
+
 # ---------------------------------------------------------------- GPU: the CUDA path is held to the fixture
+@pytest.mark.gpu
+def test_gpu_frame_features(g):
+    import __graft_entry__ as entry
+    from loqa_hub_b200 import _lib as L
+    from loqa_hub_b200 import api
+    entry.build()
+    with api.Context(device=0, max_streams=8, max_batch_msgs=16, ring_bytes=1 << 20, arena_samples=4_000,
+                     wake_samples_max=400, mode=L.DO_ALL, want_frames=True) as c:
+        msgs = g["frames"]
+        res, fr = c.ingest([bytes.fromhex(m["pcm_hex"]) for m in msgs], list(range(len(msgs))),
+                           [L.MSG_FIRST] * len(msgs))
+        pos = 0
+        for m in msgs:
+            want = _want_frames(m)
+            assert [_frame_tuple(a) for a in fr[pos:pos + len(want)]] == want
+            pos += len(want)
+        assert pos == len(fr)
+
+
 @pytest.mark.gpu
 def test_gpu_arbitration_kernels(g):
     import torch

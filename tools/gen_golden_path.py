@@ -114,8 +114,25 @@ for c in utt_chunks:
 utterance = {"chunks_hex": [c.hex() for c in utt_chunks], "running_sha256": running,
              "samples_sha256": hashlib.sha256(np.concatenate([npm.bytes_to_float32(c) for c in utt_chunks]).tobytes()).hexdigest()}
 
+# ------------------------------------------------------------------ 20 ms framing (N1): A2 per 320-sample frame
+frame_msgs = []
+for n in (1000, 320, 321, 5):
+    x = rng.integers(-25000, 25000, size=n)
+    x[rng.random(n) < 0.2] = 0
+    data = x.astype("<i2").tobytes()
+    s = npm.bytes_to_float32(data)
+    frs = []
+    for off in range(0, n, 320):
+        fr = s[off:off + 320]
+        rms, sumsq = npm.signal_strength(fr)
+        frs.append({"n_samples": int(fr.size), "sumsq_f64_hex": f64_hex(sumsq), "rms_f64_hex": f64_hex(rms),
+                    "nonzero": int((fr != 0).sum()), "peak_bits": int(np.abs(fr).max().view(np.uint32)),
+                    "vad": int(rms > 0.01)})
+    frame_msgs.append({"pcm_hex": data.hex(), "frames": frs})
+
 out = os.path.join(ROOT, "tests", "golden", "path_golden.json")
 with open(out, "w") as fh:
     json.dump({"generator": "tools/gen_golden_path.py", "tap_bits": [int(b) for b in taps.view(np.uint32)],
-               "arbitration": windows, "resample": streams, "wav": wav, "utterance": utterance}, fh, indent=0)
+               "arbitration": windows, "resample": streams, "wav": wav, "utterance": utterance,
+               "frames": frame_msgs}, fh, indent=0)
 print("wrote", out, os.path.getsize(out), "bytes")
