@@ -479,6 +479,26 @@ int ga_stream_audio_metadata(ga_ctx *ctx, uint32_t stream_id, int sample_rate, i
 /* "sha256:<hex>" of a 32-byte digest; pure host code. */
 void ga_format_audio_hash(const uint8_t digest[32], char *audio_hash);
 
+/* ===================================================================== cluster
+ * Several contexts of ONE process, one per GPU — how a single hub process drives an 8-GPU box.
+ * A collision group is assigned to a shard when its window opens (startArbitrationWindow,
+ * audio_service.go:408); relays that joined through another shard leave the window spanning GPUs.
+ * ga_cluster_arbitrate is performArbitration (:505-571) for any mix of local and spanning windows:
+ * member m is stream stream_ids[m] of context shard_ids[m] (join order per window, as in
+ * ga_arbitrate); a window is homed on the shard of its FIRST member.  One fused launch per GPU
+ * (ga_k_arbitrate_p2p): every shard scores its own relays, stores the scores of relays homed
+ * elsewhere into the home shard's inbox over NVLink and raises a flag there; the home kernel
+ * waits for its senders (bounded) and selects.  Outputs are indexed like the inputs: winner_idx[w]
+ * is a member index or 0xFFFFFFFF for an empty window.  max_guests bounds the remote relays one
+ * shard may receive per call.  The contexts must sit on distinct, peer-accessible devices and
+ * outlive the cluster.  GA_ERR_COMM: no peer path, or a peer's scores did not arrive in time. */
+typedef struct ga_cluster ga_cluster;
+int  ga_cluster_create(ga_ctx *const *ctxs, uint32_t n_ctx, uint32_t max_guests, ga_cluster **out);
+void ga_cluster_destroy(ga_cluster *cl);
+int  ga_cluster_arbitrate(ga_cluster *cl, const uint32_t *seg_offsets, uint32_t n_windows,
+                          const uint32_t *shard_ids, const uint32_t *stream_ids, const uint8_t *status_in,
+                          uint32_t *winner_idx, double *scores, uint8_t *status_out);
+
 /* ===================================================================== utilities */
 
 /* Synthetic relay PCM: integer-only, bit-identical on host and device.

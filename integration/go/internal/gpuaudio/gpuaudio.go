@@ -121,3 +121,34 @@ func (x *Ctx) Samples(stream uint32) ([]float32, error) {
 	}
 	return out, nil
 }
+
+// Cluster arbitrates windows whose relays sit on different GPUs of this process (one Ctx per GPU).
+type Cluster struct{ c *C.ga_cluster }
+
+func NewCluster(ctxs []*Ctx, maxGuests int) (*Cluster, error) {
+	hs := make([]*C.ga_ctx, len(ctxs))
+	for i, x := range ctxs {
+		hs[i] = x.c
+	}
+	var c *C.ga_cluster
+	if rc := C.ga_cluster_create(&hs[0], C.uint32_t(len(hs)), C.uint32_t(maxGuests), &c); rc != 0 {
+		return nil, lastErr(rc)
+	}
+	return &Cluster{c}, nil
+}
+
+func (k *Cluster) Close() { C.ga_cluster_destroy(k.c) }
+
+// Arbitrate is performArbitration for windows across GPUs: member m is stream streamIDs[m] of
+// context shardIDs[m], in join order per window.
+func (k *Cluster) Arbitrate(segOffsets, shardIDs, streamIDs []uint32, statusIn []uint8) (winner []uint32, scores []float64, statusOut []uint8, err error) {
+	nw := len(segOffsets) - 1
+	winner, scores, statusOut = make([]uint32, nw), make([]float64, len(streamIDs)), make([]uint8, len(streamIDs))
+	rc := C.ga_cluster_arbitrate(k.c, (*C.uint32_t)(&segOffsets[0]), C.uint32_t(nw), (*C.uint32_t)(&shardIDs[0]),
+		(*C.uint32_t)(&streamIDs[0]), (*C.uint8_t)(&statusIn[0]), (*C.uint32_t)(&winner[0]), (*C.double)(&scores[0]),
+		(*C.uint8_t)(&statusOut[0]))
+	if rc != 0 {
+		err = lastErr(rc)
+	}
+	return
+}

@@ -85,6 +85,9 @@ SYMBOLS = {
     "ga_set_audio_metadata": (_i32, [_vp, _vp, C.c_size_t, _i32, _i32, C.POINTER(C.c_double), C.c_char_p]),
     "ga_stream_audio_metadata": (_i32, [_vp, _u32, _i32, _i32, C.POINTER(C.c_double), C.c_char_p]),
     "ga_format_audio_hash": (None, [_vp, C.c_char_p]),
+    "ga_cluster_create": (_i32, [_vp, _u32, _u32, C.POINTER(_vp)]),
+    "ga_cluster_destroy": (None, [_vp]),
+    "ga_cluster_arbitrate": (_i32, [_vp, _vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ga_submit_ticks": (_i32, [_vp, _u64, _u32, _u32, _u32, _vp, _vp, C.POINTER(_u64)]),
     "ga_wait": (_i32, [_vp, _u64, _vp, _vp]),
     "ga_wait_view": (_i32, [_vp, _u64, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_u32), C.POINTER(_u32)]),

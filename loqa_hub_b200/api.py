@@ -296,3 +296,40 @@ class Context:
         out = np.zeros(32, dtype=np.uint8)
         check(load().ga_sha256(self._h, ptr(b), b.size, ptr(out)))
         return out.tobytes()
+
+
+class Cluster:
+    """ga_cluster: several contexts of this process, one per GPU; arbitration of windows whose
+    relays sit on different GPUs in one fused launch per GPU (peer stores over NVLink)."""
+
+    def __init__(self, contexts, max_guests=4096):
+        self.contexts = list(contexts)
+        arr = (C.c_void_p * len(self.contexts))(*[c._h for c in self.contexts])
+        self._h = C.c_void_p()
+        check(load().ga_cluster_create(arr, len(self.contexts), max_guests, C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            load().ga_cluster_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def arbitrate(self, seg_offsets, shard_ids, stream_ids, status_in=None, scores_in=None):
+        seg = np.ascontiguousarray(seg_offsets, dtype=np.uint32)
+        nw = seg.size - 1
+        sh = np.ascontiguousarray(shard_ids, dtype=np.uint32)
+        sid = np.ascontiguousarray(stream_ids, dtype=np.uint32)
+        nm = sid.size
+        st = np.full(nm, L.RELAY_CONTENDING, np.uint8) if status_in is None else \
+            np.ascontiguousarray(status_in, dtype=np.uint8)
+        scores = np.zeros(nm, np.float64) if scores_in is None else np.array(scores_in, dtype=np.float64)
+        winner = np.zeros(max(nw, 0), np.uint32)
+        st_out = np.zeros(nm, np.uint8)
+        check(load().ga_cluster_arbitrate(self._h, ptr(seg), max(nw, 0), ptr(sh), ptr(sid), ptr(st), ptr(winner),
+                                          ptr(scores), ptr(st_out)))
+        return winner, scores, st_out

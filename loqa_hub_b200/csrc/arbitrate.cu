@@ -259,10 +259,12 @@ extern "C" int ga_k_arbitrate_p2p(const ga_p2p_args *args, void *stream)
     using namespace ga;
     if (!args) { set_error("ga_k_arbitrate_p2p: NULL argument"); return GA_ERR_ARG; }
     const ga_p2p_args &a = *args;
-    if (a.n_windows == 0) return GA_OK;
+    // a shard without windows of its own still has to score and send its guests
+    if (a.n_windows == 0 && a.n_guests == 0 && a.n_notify == 0) return GA_OK;
     const uint32_t n_all = a.n_home_members + a.n_guests;
-    if (!a.d_seg_offsets || !a.d_winner || !a.d_counter || !a.d_error ||
-        (n_all && (!a.d_samples || !a.d_wake_off || !a.d_wake_n || !a.d_status_in || !a.d_scores || !a.d_status_out)) ||
+    if ((a.n_windows && (!a.d_seg_offsets || !a.d_winner)) || !a.d_counter || !a.d_error ||
+        (n_all && (!a.d_samples || !a.d_wake_off || !a.d_wake_n || !a.d_status_in || !a.d_scores)) ||
+        (a.n_home_members && !a.d_status_out) ||
         (a.n_guests && !a.d_guest_dst) || (a.n_notify && !a.d_notify) || (a.n_wait && !a.d_wait) ||
         (a.n_in && (!a.d_inbox || !a.d_route_dst))) {
         set_error("ga_k_arbitrate_p2p: NULL array in arguments");

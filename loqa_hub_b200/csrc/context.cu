@@ -1300,3 +1300,293 @@ extern "C" int ga_synth_fill_batch_device(void *d_pcm, uint64_t seed, uint32_t g
     GA_CHECK_LAUNCH("synth_batch_kernel");
     return GA_OK;
 }
+
+// ---------------------------------------------------------------- cluster: one process, several GPUs
+// The hub is ONE process; on an 8-GPU box it holds one context per GPU and assigns a collision group
+// to a shard when its window opens.  When the relays of a window ended up on different shards,
+// performArbitration (audio_service.go:505-571) needs the scores of all of them on one GPU: every
+// shard scores its own relays, writes the scores of relays whose window is homed elsewhere straight
+// into that shard's inbox over NVLink (peer stores from inside the kernel) and raises a flag there;
+// the home shard's kernel waits for its senders' flags and runs the selection — ONE launch per GPU
+// (ga_k_arbitrate_p2p), no host round trip between scoring and selection.
+namespace ga {
+
+struct ClusterShard {
+    ga_ctx *ctx = nullptr;
+    int dev = 0;
+    cudaStream_t stream = nullptr;
+    uint8_t *region = nullptr;            // inbox[2][cap] f64 | flags[n_shards] u64 | counter, error u32
+    uint8_t *scratch = nullptr;           // grow-only device tables
+    size_t scratch_bytes = 0;
+    // per-call host tables
+    std::vector<uint64_t> off, guest_dst, notify, wait;
+    std::vector<uint32_t> cnt, seg, route_dst, member_of, windows;
+    std::vector<uint8_t> st;
+    std::vector<double> sc;
+    uint32_t n_home = 0, n_guests = 0;
+    struct Incoming { uint32_t from, member, pos; };
+    std::vector<Incoming> incoming;
+    std::vector<uint32_t> win_out;
+    std::vector<uint8_t> st_out;
+    uint32_t err = 0;
+    bool launched = false;
+    size_t o_win = 0, o_sc = 0, o_so = 0;
+};
+
+}  // namespace ga
+
+struct ga_cluster {
+    std::vector<ga::ClusterShard> shards;
+    uint32_t cap = 0;                      // inbox slots per shard and parity
+    uint64_t parity_stride = 0, flags_off = 0, ctl_off = 0, region_bytes = 0;
+    uint64_t epoch = 0;
+    std::mutex mu;
+};
+
+extern "C" void ga_cluster_destroy(ga_cluster *cl)
+{
+    if (!cl) return;
+    for (auto &s : cl->shards) {
+        cudaSetDevice(s.dev);
+        if (s.stream) { cudaStreamSynchronize(s.stream); cudaStreamDestroy(s.stream); }
+        if (s.region) cudaFree(s.region);
+        if (s.scratch) cudaFree(s.scratch);
+    }
+    delete cl;
+}
+
+extern "C" int ga_cluster_create(ga_ctx *const *ctxs, uint32_t n_ctx, uint32_t max_guests, ga_cluster **out)
+{
+    if (!ctxs || !out || n_ctx == 0 || n_ctx > 64) { set_error("ga_cluster_create: bad argument"); return GA_ERR_ARG; }
+    *out = nullptr;
+    for (uint32_t i = 0; i < n_ctx; i++) {
+        if (!ctxs[i]) { set_error("ga_cluster_create: NULL context %u", i); return GA_ERR_ARG; }
+        if (!(ctxs[i]->cfg.mode & GA_DO_CONVERT)) { set_error("ga_cluster_create: context %u does not materialise samples", i); return GA_ERR_STATE; }
+        for (uint32_t j = 0; j < i; j++)
+            if (ctxs[j]->cfg.device == ctxs[i]->cfg.device) {
+                // two waiting kernels on one GPU could starve each other: one shard per device
+                set_error("ga_cluster_create: contexts %u and %u share device %d", j, i, ctxs[i]->cfg.device);
+                return GA_ERR_ARG;
+            }
+    }
+    ga_cluster *cl = new (std::nothrow) ga_cluster;
+    if (!cl) { set_error("ga_cluster_create: out of host memory"); return GA_ERR_NOMEM; }
+    cl->cap = max_guests ? max_guests : 1;
+    cl->parity_stride = 8ull * cl->cap;
+    cl->flags_off = 2 * cl->parity_stride;
+    cl->ctl_off = cl->flags_off + 8ull * n_ctx;
+    cl->region_bytes = cl->ctl_off + 16;
+    try { cl->shards.resize(n_ctx); } catch (...) { delete cl; set_error("ga_cluster_create: out of host memory"); return GA_ERR_NOMEM; }
+    auto fail = [&](int code) { ga_cluster_destroy(cl); return code; };
+    for (uint32_t i = 0; i < n_ctx; i++) {
+        ClusterShard &s = cl->shards[i];
+        s.ctx = ctxs[i];
+        s.dev = ctxs[i]->cfg.device;
+        cudaError_t e = cudaSetDevice(s.dev);
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void **>(&s.region), cl->region_bytes);
+        if (e == cudaSuccess) e = cudaMemset(s.region, 0, cl->region_bytes);
+        if (e != cudaSuccess) { cudaGetLastError(); set_error("ga_cluster_create: device %d: %s", s.dev, cudaGetErrorString(e)); return fail(GA_ERR_CUDA); }
+        for (uint32_t j = 0; j < n_ctx; j++) {
+            if (j == i) continue;
+            int can = 0;
+            e = cudaDeviceCanAccessPeer(&can, s.dev, ctxs[j]->cfg.device);
+            if (e != cudaSuccess || !can) {
+                cudaGetLastError();
+                set_error("ga_cluster_create: device %d cannot address device %d (no NVLink / PCIe peer path)", s.dev, ctxs[j]->cfg.device);
+                return fail(GA_ERR_COMM);
+            }
+            e = cudaDeviceEnablePeerAccess(ctxs[j]->cfg.device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+                cudaGetLastError();
+                set_error("ga_cluster_create: cudaDeviceEnablePeerAccess(%d -> %d): %s", s.dev, ctxs[j]->cfg.device, cudaGetErrorString(e));
+                return fail(GA_ERR_COMM);
+            }
+            cudaGetLastError();
+        }
+    }
+    for (auto &s : cl->shards) { cudaSetDevice(s.dev); cudaDeviceSynchronize(); }
+    *out = cl;
+    return GA_OK;
+}
+
+extern "C" int ga_cluster_arbitrate(ga_cluster *cl, const uint32_t *seg_offsets, uint32_t n_windows,
+                                    const uint32_t *shard_ids, const uint32_t *stream_ids, const uint8_t *status_in,
+                                    uint32_t *winner_idx, double *scores, uint8_t *status_out)
+{
+    if (!cl) { set_error("ga_cluster_arbitrate: NULL cluster"); return GA_ERR_ARG; }
+    if (n_windows == 0) return GA_OK;
+    if (!seg_offsets || !winner_idx) { set_error("ga_cluster_arbitrate: NULL argument"); return GA_ERR_ARG; }
+    const uint32_t n_members = seg_offsets[n_windows];
+    if (n_members && (!shard_ids || !stream_ids || !status_in || !scores || !status_out)) { set_error("ga_cluster_arbitrate: NULL member array"); return GA_ERR_ARG; }
+    const uint32_t n_sh = static_cast<uint32_t>(cl->shards.size());
+    for (uint32_t w = 0; w < n_windows; w++)
+        if (seg_offsets[w] > seg_offsets[w + 1]) { set_error("ga_cluster_arbitrate: seg_offsets not monotone at %u", w); return GA_ERR_ARG; }
+    for (uint32_t m = 0; m < n_members; m++)
+        if (shard_ids[m] >= n_sh || stream_ids[m] >= cl->shards[shard_ids[m]].ctx->cfg.max_streams) {
+            set_error("ga_cluster_arbitrate: member %u: shard %u / stream %u out of range", m, shard_ids[m], stream_ids[m]);
+            return GA_ERR_ARG;
+        }
+    std::lock_guard<std::mutex> lk(cl->mu);
+
+    // ---- plan: a window is homed on the shard of its first member (join order)
+    for (auto &s : cl->shards) {
+        s.off.clear(); s.cnt.clear(); s.st.clear(); s.sc.clear(); s.seg.assign(1, 0); s.member_of.clear(); s.windows.clear();
+        s.incoming.clear(); s.guest_dst.clear(); s.notify.clear(); s.wait.clear(); s.route_dst.clear();
+        s.n_home = s.n_guests = 0; s.err = 0;
+    }
+    auto wake_of = [&](uint32_t shard, uint32_t sid, uint64_t &off, uint32_t &cnt) {
+        ga_ctx *c = cl->shards[shard].ctx;
+        std::lock_guard<std::mutex> g(c->mu);
+        off = static_cast<uint64_t>(sid) * c->cfg.arena_samples;
+        cnt = static_cast<uint32_t>(c->streams[sid].wake_n);
+    };
+    for (uint32_t w = 0; w < n_windows; w++) {
+        const uint32_t lo = seg_offsets[w], hi = seg_offsets[w + 1];
+        if (lo == hi) { winner_idx[w] = 0xffffffffu; continue; }
+        const uint32_t h = shard_ids[lo];
+        ClusterShard &s = cl->shards[h];
+        s.windows.push_back(w);
+        for (uint32_t m = lo; m < hi; m++) {
+            uint64_t off = 0; uint32_t cnt = 0;
+            const uint32_t pos = static_cast<uint32_t>(s.off.size());
+            if (shard_ids[m] == h) wake_of(h, stream_ids[m], off, cnt);
+            else if (status_in[m] == GA_RELAY_CONTENDING) s.incoming.push_back({shard_ids[m], m, pos});
+            s.off.push_back(off); s.cnt.push_back(cnt); s.st.push_back(status_in[m]); s.sc.push_back(scores[m]);
+            s.member_of.push_back(m);
+        }
+        s.seg.push_back(static_cast<uint32_t>(s.off.size()));
+    }
+    for (uint32_t h = 0; h < n_sh; h++) {
+        ClusterShard &s = cl->shards[h];
+        s.n_home = static_cast<uint32_t>(s.off.size());
+        if (s.incoming.size() > cl->cap) {
+            set_error("ga_cluster_arbitrate: shard %u receives %zu remote relays, cluster was created for %u", h, s.incoming.size(), cl->cap);
+            return GA_ERR_OVERFLOW;
+        }
+    }
+    // guests: the k-th remote relay of home shard h lands in inbox slot k there
+    std::vector<uint8_t> sends(static_cast<size_t>(n_sh) * n_sh, 0);     // sends[from * n + to]
+    for (uint32_t h = 0; h < n_sh; h++) {
+        ClusterShard &home = cl->shards[h];
+        for (uint32_t k = 0; k < home.incoming.size(); k++) {
+            const auto &in = home.incoming[k];
+            ClusterShard &g = cl->shards[in.from];
+            uint64_t off; uint32_t cnt;
+            wake_of(in.from, stream_ids[in.member], off, cnt);
+            g.off.push_back(off); g.cnt.push_back(cnt); g.st.push_back(GA_RELAY_CONTENDING); g.sc.push_back(0.0);
+            g.guest_dst.push_back(reinterpret_cast<uint64_t>(home.region) + 8ull * k);
+            g.n_guests++;
+            home.route_dst.push_back(in.pos);
+            sends[static_cast<size_t>(in.from) * n_sh + h] = 1;
+        }
+    }
+    for (uint32_t a = 0; a < n_sh; a++)
+        for (uint32_t b = 0; b < n_sh; b++)
+            if (sends[static_cast<size_t>(a) * n_sh + b]) {
+                cl->shards[a].notify.push_back(reinterpret_cast<uint64_t>(cl->shards[b].region) + cl->flags_off + 8ull * a);
+                cl->shards[b].wait.push_back(reinterpret_cast<uint64_t>(cl->shards[b].region) + cl->flags_off + 8ull * a);
+            }
+
+    // ---- one launch per GPU; nothing is waited for until all of them are queued
+    const uint64_t epoch = ++cl->epoch;
+    auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
+    int rc = GA_OK;
+    for (uint32_t i = 0; i < n_sh && rc == GA_OK; i++) {
+        ClusterShard &s = cl->shards[i];
+        const size_t n_all = s.off.size(), nw = s.windows.size();
+        if (n_all == 0 && s.notify.empty()) continue;
+        auto step = [&]() -> int {
+            GA_CUDA_TRY(cudaSetDevice(s.dev));
+            const size_t o_off = 0, o_cnt = o_off + up(8 * n_all), o_st = o_cnt + up(4 * n_all), o_sc = o_st + up(n_all),
+                         o_seg = o_sc + up(8 * n_all), o_win = o_seg + up(4 * (nw + 1)), o_so = o_win + up(4 * nw),
+                         o_gd = o_so + up(s.n_home), o_no = o_gd + up(8 * s.guest_dst.size()), o_wa = o_no + up(8 * s.notify.size()),
+                         o_rd = o_wa + up(8 * s.wait.size()), need = o_rd + up(4 * s.route_dst.size()) + 256;
+            if (need > s.scratch_bytes) {
+                GA_CUDA_TRY(cudaStreamSynchronize(s.stream));
+                if (s.scratch) cudaFree(s.scratch);
+                s.scratch = nullptr; s.scratch_bytes = 0;
+                cudaError_t e = cudaMalloc(reinterpret_cast<void **>(&s.scratch), need + need / 2);
+                if (e != cudaSuccess) { cudaGetLastError(); set_error("ga_cluster_arbitrate: cudaMalloc failed: %s", cudaGetErrorString(e)); return GA_ERR_NOMEM; }
+                s.scratch_bytes = need + need / 2;
+            }
+            uint8_t *b = s.scratch;
+            auto put = [&](size_t o, const void *src, size_t bytes) -> int {
+                if (bytes) GA_CUDA_TRY(cudaMemcpyAsync(b + o, src, bytes, cudaMemcpyHostToDevice, s.stream));
+                return GA_OK;
+            };
+            {   // the wake-word buffers must be complete: wait for every ticket of this context in flight
+                std::lock_guard<std::mutex> g(s.ctx->mu);
+                int r = join_inflight(s.ctx, s.stream);
+                if (r) return r;
+            }
+            int r;
+            if ((r = put(o_off, s.off.data(), 8 * n_all)) || (r = put(o_cnt, s.cnt.data(), 4 * n_all)) ||
+                (r = put(o_st, s.st.data(), n_all)) || (r = put(o_sc, s.sc.data(), 8 * n_all)) ||
+                (r = put(o_seg, s.seg.data(), 4 * (nw + 1))) || (r = put(o_gd, s.guest_dst.data(), 8 * s.guest_dst.size())) ||
+                (r = put(o_no, s.notify.data(), 8 * s.notify.size())) || (r = put(o_wa, s.wait.data(), 8 * s.wait.size())) ||
+                (r = put(o_rd, s.route_dst.data(), 4 * s.route_dst.size())))
+                return r;
+            ga_p2p_args a;
+            std::memset(&a, 0, sizeof a);
+            a.d_samples = s.ctx->d_arena;
+            a.d_wake_off = reinterpret_cast<uint64_t *>(b + o_off); a.d_wake_n = reinterpret_cast<uint32_t *>(b + o_cnt);
+            a.d_status_in = b + o_st; a.d_seg_offsets = reinterpret_cast<uint32_t *>(b + o_seg);
+            a.d_scores = reinterpret_cast<double *>(b + o_sc); a.d_winner = reinterpret_cast<uint32_t *>(b + o_win);
+            a.d_status_out = b + o_so;
+            a.d_guest_dst = reinterpret_cast<uint64_t *>(b + o_gd); a.d_notify = reinterpret_cast<uint64_t *>(b + o_no);
+            a.d_wait = reinterpret_cast<uint64_t *>(b + o_wa); a.d_inbox = reinterpret_cast<double *>(s.region);
+            a.d_route_dst = reinterpret_cast<uint32_t *>(b + o_rd);
+            a.d_counter = reinterpret_cast<uint32_t *>(s.region + cl->ctl_off);
+            a.d_error = reinterpret_cast<uint32_t *>(s.region + cl->ctl_off + 4);
+            a.inbox_parity_stride = cl->parity_stride;
+            a.epoch = epoch;
+            a.timeout_cycles = 4'000'000'000ll;          // ~2 s: a peer that never launched must not hang this GPU
+            a.n_windows = static_cast<uint32_t>(nw); a.n_home_members = s.n_home; a.n_guests = s.n_guests;
+            a.n_notify = static_cast<uint32_t>(s.notify.size()); a.n_wait = static_cast<uint32_t>(s.wait.size());
+            a.n_in = static_cast<uint32_t>(s.route_dst.size());
+            r = ga_k_arbitrate_p2p(&a, s.stream);
+            if (r) return r;
+            // results are fetched only after EVERY shard's kernel is queued: a copy into pageable
+            // memory blocks the host until this shard's kernel is done, and that kernel may be
+            // waiting for a shard that is launched later in this loop
+            s.launched = true; s.o_win = o_win; s.o_sc = o_sc; s.o_so = o_so;
+            return GA_OK;
+        };
+        rc = step();
+    }
+    // collect (also after a failure: the shards already launched finish on their own, by data or by timeout)
+    for (uint32_t i = 0; i < n_sh; i++) {
+        ClusterShard &s = cl->shards[i];
+        if (!s.launched) continue;
+        s.launched = false;
+        cudaSetDevice(s.dev);
+        const size_t nw = s.windows.size();
+        s.win_out.resize(nw); s.st_out.resize(s.n_home);
+        cudaError_t e = cudaSuccess;
+        if (nw) e = cudaMemcpyAsync(s.win_out.data(), s.scratch + s.o_win, 4 * nw, cudaMemcpyDeviceToHost, s.stream);
+        if (e == cudaSuccess && s.n_home) e = cudaMemcpyAsync(s.sc.data(), s.scratch + s.o_sc, 8ull * s.n_home, cudaMemcpyDeviceToHost, s.stream);
+        if (e == cudaSuccess && s.n_home) e = cudaMemcpyAsync(s.st_out.data(), s.scratch + s.o_so, s.n_home, cudaMemcpyDeviceToHost, s.stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(&s.err, s.region + cl->ctl_off + 4, 4, cudaMemcpyDeviceToHost, s.stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s.stream);
+        if (e != cudaSuccess && rc == GA_OK) { cudaGetLastError(); set_error("ga_cluster_arbitrate: device %d: %s", s.dev, cudaGetErrorString(e)); rc = GA_ERR_CUDA; }
+        if (s.err && rc == GA_OK) {
+            set_error("ga_cluster_arbitrate: shard %u timed out waiting for a peer's scores", i);
+            rc = GA_ERR_COMM;
+        }
+        if (s.err) { cudaMemsetAsync(s.region + cl->ctl_off + 4, 0, 4, s.stream); cudaStreamSynchronize(s.stream); s.err = 0; }
+    }
+    if (rc) return rc;
+    for (auto &s : cl->shards) {
+        for (size_t k = 0; k < s.windows.size(); k++) {
+            const uint32_t w = s.windows[k], p = s.win_out[k];
+            winner_idx[w] = p == 0xffffffffu ? 0xffffffffu : s.member_of[p];
+        }
+        for (uint32_t p = 0; p < s.n_home; p++) {
+            const uint32_t m = s.member_of[p];
+            if (status_in[m] == GA_RELAY_CONTENDING) scores[m] = s.sc[p];   // :528; skipped relays keep theirs (:522-524)
+            status_out[m] = s.st_out[p];
+        }
+    }
+    return GA_OK;
+}
