@@ -289,6 +289,7 @@ int ga_p2p_free(void *d_ptr);
  * Host-buffer layer: what internal/gpuaudio binds.  One context per GPU.        */
 
 typedef struct ga_ctx ga_ctx;
+typedef struct ga_cluster ga_cluster;   /* several contexts of one process: see "cluster" below */
 
 typedef struct ga_config {
     int32_t  device;            /* CUDA ordinal                                        */
@@ -449,6 +450,18 @@ int  ga_hub_set_relay_status(ga_hub *hub, const char *relay_id, int status);   /
 int  ga_hub_complete_request(ga_hub *hub, const char *relay_id);               /* collision_detection_test.go:361-369 */
 int  ga_hub_cleanup_relay(ga_hub *hub, const char *relay_id);                  /* cleanupRelay :916-923 */
 int  ga_hub_active_streams(ga_hub *hub, uint32_t *n);                          /* len(as.activeStreams) */
+/* The same hub over every GPU of the box (one process, one context per GPU, held by `cluster`,
+ * which must outlive the hub): ga_hub_connect places a relay on shard group % nGPU so that a
+ * group's window normally stays on one GPU; ga_hub_connect_on forces a shard (the window then
+ * spans GPUs and is arbitrated through ga_cluster_arbitrate).  Chunks go to the relay's own GPU;
+ * ga_hub_flush submits one batch per GPU.  max_streams_per_shard <= the contexts' max_streams. */
+int  ga_hub_create_cluster(ga_cluster *cluster, uint32_t max_streams_per_shard, uint64_t window_duration_us,
+                           ga_hub **out);
+int  ga_hub_connect_on(ga_hub *hub, const char *relay_id, uint32_t group, uint32_t shard, uint32_t *slot);
+int  ga_hub_relay_shard(ga_hub *hub, const char *relay_id, uint32_t *shard);
+/* ga_fetch_wav for a relay, from whichever GPU holds its audio. */
+int  ga_hub_fetch_wav(ga_hub *hub, const char *relay_id, uint32_t sample_rate, uint8_t *out, size_t cap,
+                      size_t *n_bytes);
 
 /* --------------------------------------------------------------- one-shot mirrors
  * Same argument meaning and degenerate-input behaviour as the Go functions; used by
@@ -492,12 +505,13 @@ void ga_format_audio_hash(const uint8_t digest[32], char *audio_hash);
  * is a member index or 0xFFFFFFFF for an empty window.  max_guests bounds the remote relays one
  * shard may receive per call.  The contexts must sit on distinct, peer-accessible devices and
  * outlive the cluster.  GA_ERR_COMM: no peer path, or a peer's scores did not arrive in time. */
-typedef struct ga_cluster ga_cluster;
 int  ga_cluster_create(ga_ctx *const *ctxs, uint32_t n_ctx, uint32_t max_guests, ga_cluster **out);
 void ga_cluster_destroy(ga_cluster *cl);
 int  ga_cluster_arbitrate(ga_cluster *cl, const uint32_t *seg_offsets, uint32_t n_windows,
                           const uint32_t *shard_ids, const uint32_t *stream_ids, const uint8_t *status_in,
                           uint32_t *winner_idx, double *scores, uint8_t *status_out);
+uint32_t ga_cluster_size(const ga_cluster *cl);
+ga_ctx  *ga_cluster_context(const ga_cluster *cl, uint32_t shard);
 
 /* ===================================================================== utilities */
 

@@ -85,6 +85,12 @@ SYMBOLS = {
     "ga_set_audio_metadata": (_i32, [_vp, _vp, C.c_size_t, _i32, _i32, C.POINTER(C.c_double), C.c_char_p]),
     "ga_stream_audio_metadata": (_i32, [_vp, _u32, _i32, _i32, C.POINTER(C.c_double), C.c_char_p]),
     "ga_format_audio_hash": (None, [_vp, C.c_char_p]),
+    "ga_cluster_size": (_u32, [_vp]),
+    "ga_cluster_context": (_vp, [_vp, _u32]),
+    "ga_hub_create_cluster": (_i32, [_vp, _u32, _u64, C.POINTER(_vp)]),
+    "ga_hub_connect_on": (_i32, [_vp, C.c_char_p, _u32, _u32, C.POINTER(_u32)]),
+    "ga_hub_relay_shard": (_i32, [_vp, C.c_char_p, C.POINTER(_u32)]),
+    "ga_hub_fetch_wav": (_i32, [_vp, C.c_char_p, _u32, _vp, C.c_size_t, C.POINTER(C.c_size_t)]),
     "ga_cluster_create": (_i32, [_vp, _u32, _u32, C.POINTER(_vp)]),
     "ga_cluster_destroy": (None, [_vp]),
     "ga_cluster_arbitrate": (_i32, [_vp, _vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp]),

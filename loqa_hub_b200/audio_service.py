@@ -30,11 +30,30 @@ class RelayInfo:
 
 class AudioService:
     def __init__(self, ctx, max_streams, window_duration_us=0):
-        """ctx: an api.Context, or None for the bookkeeping-only hub the CPU tests use."""
-        self.ctx = ctx
+        """ctx: an api.Context, None for the bookkeeping-only hub the CPU tests use, or an
+        api.Cluster — one hub over every GPU of the box (max_streams is then per GPU)."""
         self._h = C.c_void_p()
+        if isinstance(ctx, api.Cluster):
+            self.cluster, self.ctx = ctx, None
+            L.check(L.load().ga_hub_create_cluster(ctx._h, max_streams, window_duration_us, C.byref(self._h)))
+            return
+        self.cluster, self.ctx = None, ctx
         L.check(L.load().ga_hub_create(ctx._h if ctx is not None else None, max_streams, window_duration_us,
                                        C.byref(self._h)))
+
+    def connect_on(self, relay_id, group, shard):
+        """ga_hub_connect_on: the relay's audio lives on GPU `shard` whatever its group."""
+        slot = C.c_uint32()
+        L.check(L.load().ga_hub_connect_on(self._h, relay_id.encode(), group, shard, C.byref(slot)))
+        return slot.value
+
+    def relay_shard(self, relay_id):
+        sh = C.c_uint32()
+        L.check(L.load().ga_hub_relay_shard(self._h, relay_id.encode(), C.byref(sh)))
+        return sh.value
+
+    def relay_context(self, relay_id):
+        return self.cluster.contexts[self.relay_shard(relay_id)] if self.cluster else self.ctx
 
     def close(self):
         if self._h:
@@ -110,9 +129,8 @@ class AudioService:
         return n.value
 
     def fetch_wav(self, relay_id, sample_rate=16000):
-        slot = self.relay(relay_id).slot
         n = C.c_size_t()
-        L.check(L.load().ga_fetch_wav(self.ctx._h, slot, sample_rate, None, 0, C.byref(n)))
+        L.check(L.load().ga_hub_fetch_wav(self._h, relay_id.encode(), sample_rate, None, 0, C.byref(n)))
         out = np.zeros(n.value, dtype=np.uint8)
-        L.check(L.load().ga_fetch_wav(self.ctx._h, slot, sample_rate, L.ptr(out), out.size, C.byref(n)))
+        L.check(L.load().ga_hub_fetch_wav(self._h, relay_id.encode(), sample_rate, L.ptr(out), out.size, C.byref(n)))
         return out.tobytes()

@@ -1410,6 +1410,12 @@ extern "C" int ga_cluster_create(ga_ctx *const *ctxs, uint32_t n_ctx, uint32_t m
     return GA_OK;
 }
 
+extern "C" uint32_t ga_cluster_size(const ga_cluster *cl) { return cl ? static_cast<uint32_t>(cl->shards.size()) : 0u; }
+extern "C" ga_ctx *ga_cluster_context(const ga_cluster *cl, uint32_t shard)
+{
+    return (cl && shard < cl->shards.size()) ? cl->shards[shard].ctx : nullptr;
+}
+
 extern "C" int ga_cluster_arbitrate(ga_cluster *cl, const uint32_t *seg_offsets, uint32_t n_windows,
                                     const uint32_t *shard_ids, const uint32_t *stream_ids, const uint8_t *status_in,
                                     uint32_t *winner_idx, double *scores, uint8_t *status_out)

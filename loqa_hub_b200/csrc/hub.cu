@@ -29,7 +29,8 @@ namespace {
 struct Relay {                       // RelayStream :44-53
     std::string id;
     uint32_t group = 0;
-    uint32_t slot = 0;               // ga_ctx stream slot: WakeWordSignal / SpeechAudio live on the GPU
+    uint32_t shard = 0;              // which GPU's context holds the relay's audio
+    uint32_t slot = 0;               // ga_ctx stream slot there: WakeWordSignal / SpeechAudio live on the GPU
     int status = GA_RELAY_CONNECTED; // :56-63
     double signal_strength = 0.0;    // :50
     bool cancel_closed = false;      // close(relay.CancelChannel) :561
@@ -51,15 +52,19 @@ struct Window {                      // ArbitrationWindow :66-73
 }  // namespace
 
 struct ga_hub {
-    ga_ctx *ctx = nullptr;
+    // no context: bookkeeping only; one: single GPU; several (with their cluster): one hub process
+    // driving a multi-GPU box, relays placed by collision group, windows may span GPUs
+    std::vector<ga_ctx *> ctxs;
+    ga_cluster *cluster = nullptr;
     uint64_t window_duration_us = 300000;                 // arbitrationWindowDuration, 300 ms (:243)
     std::unordered_map<std::string, Relay> relays;
     std::map<uint64_t, Window> windows;                   // every window ever opened and not yet dropped
     std::unordered_map<uint32_t, uint64_t> group_window;  // as.arbitrationWindow per group (absent = nil)
-    std::vector<uint32_t> free_slots;
-    uint32_t next_slot = 0, max_slots = 0;
+    std::vector<std::vector<uint32_t>> free_slots;        // per shard
+    std::vector<uint32_t> next_slot;
+    uint32_t max_slots = 0;                               // stream slots per shard
     uint64_t next_window = 1;
-    std::vector<ga_msg> pending;                          // chunks pushed since the last flush
+    std::vector<std::vector<ga_msg>> pending;             // per shard: chunks pushed since the last flush
     std::mutex mu;
 };
 
@@ -78,8 +83,26 @@ extern "C" int ga_hub_create(ga_ctx *ctx, uint32_t max_streams, uint64_t window_
     if (!out || max_streams == 0) { set_error("ga_hub_create: bad argument"); return GA_ERR_ARG; }
     ga_hub *h = new (std::nothrow) ga_hub;
     if (!h) { set_error("ga_hub_create: out of memory"); return GA_ERR_NOMEM; }
-    h->ctx = ctx;
+    if (ctx) h->ctxs.push_back(ctx);
     h->max_slots = max_streams;
+    h->free_slots.resize(1); h->next_slot.assign(1, 0); h->pending.resize(1);
+    if (window_duration_us) h->window_duration_us = window_duration_us;
+    *out = h;
+    return GA_OK;
+}
+
+// The hub over every GPU of the box: one context per GPU held by `cluster`.
+extern "C" int ga_hub_create_cluster(ga_cluster *cluster, uint32_t max_streams_per_shard, uint64_t window_duration_us,
+                                     ga_hub **out)
+{
+    if (!out || !cluster || max_streams_per_shard == 0) { set_error("ga_hub_create_cluster: bad argument"); return GA_ERR_ARG; }
+    const uint32_t n = ga_cluster_size(cluster);
+    ga_hub *h = new (std::nothrow) ga_hub;
+    if (!h) { set_error("ga_hub_create_cluster: out of memory"); return GA_ERR_NOMEM; }
+    for (uint32_t i = 0; i < n; i++) h->ctxs.push_back(ga_cluster_context(cluster, i));
+    h->cluster = cluster;
+    h->max_slots = max_streams_per_shard;
+    h->free_slots.resize(n); h->next_slot.assign(n, 0); h->pending.resize(n);
     if (window_duration_us) h->window_duration_us = window_duration_us;
     *out = h;
     return GA_OK;
@@ -89,23 +112,50 @@ extern "C" void ga_hub_destroy(ga_hub *h) { delete h; }
 
 // A relay device opened its gRPC stream (StreamAudio :926).  It is known to the hub but not yet
 // in activeStreams — the reference only adds it there when it starts or joins a window.
-extern "C" int ga_hub_connect(ga_hub *h, const char *relay_id, uint32_t group, uint32_t *slot)
+static int connect_relay(ga_hub *h, const char *relay_id, uint32_t group, uint32_t shard, uint32_t *slot)
 {
-    if (!h || !relay_id) { set_error("ga_hub_connect: bad argument"); return GA_ERR_ARG; }
     std::lock_guard<std::mutex> lk(h->mu);
     Relay *r = find_relay(h, relay_id);
     if (!r) {
         uint32_t s;
-        if (!h->free_slots.empty()) { s = h->free_slots.back(); h->free_slots.pop_back(); }
-        else if (h->next_slot < h->max_slots) s = h->next_slot++;
-        else { set_error("ga_hub_connect: all %u stream slots are in use", h->max_slots); return GA_ERR_OVERFLOW; }
+        auto &fs = h->free_slots[shard];
+        if (!fs.empty()) { s = fs.back(); fs.pop_back(); }
+        else if (h->next_slot[shard] < h->max_slots) s = h->next_slot[shard]++;
+        else { set_error("ga_hub_connect: all %u stream slots of shard %u are in use", h->max_slots, shard); return GA_ERR_OVERFLOW; }
         Relay nr;
-        nr.id = relay_id; nr.slot = s;
+        nr.id = relay_id; nr.slot = s; nr.shard = shard;
         r = &h->relays.emplace(relay_id, nr).first->second;
     }
-    r->group = group;
+    r->group = group;                 // a known relay keeps its shard and slot: its audio lives there
     r->first_chunk = true;
     if (slot) *slot = r->slot;
+    return GA_OK;
+}
+
+extern "C" int ga_hub_connect(ga_hub *h, const char *relay_id, uint32_t group, uint32_t *slot)
+{
+    if (!h || !relay_id) { set_error("ga_hub_connect: bad argument"); return GA_ERR_ARG; }
+    // a collision group lives on shard group % nGPU, so its windows normally stay on one GPU
+    const uint32_t n = static_cast<uint32_t>(h->free_slots.size());
+    return connect_relay(h, relay_id, group, group % n, slot);
+}
+
+// A relay whose audio has to live on a given GPU (it connected through another front end, or the
+// group's shard is full): its group's windows then span GPUs.
+extern "C" int ga_hub_connect_on(ga_hub *h, const char *relay_id, uint32_t group, uint32_t shard, uint32_t *slot)
+{
+    if (!h || !relay_id) { set_error("ga_hub_connect_on: bad argument"); return GA_ERR_ARG; }
+    if (shard >= h->free_slots.size()) { set_error("ga_hub_connect_on: shard %u of %zu", shard, h->free_slots.size()); return GA_ERR_ARG; }
+    return connect_relay(h, relay_id, group, shard, slot);
+}
+
+extern "C" int ga_hub_relay_shard(ga_hub *h, const char *relay_id, uint32_t *shard)
+{
+    if (!h || !relay_id || !shard) { set_error("ga_hub_relay_shard: bad argument"); return GA_ERR_ARG; }
+    std::lock_guard<std::mutex> lk(h->mu);
+    Relay *r = find_relay(h, relay_id);
+    if (!r) { set_error("ga_hub_relay_shard: unknown relay %s", relay_id); return GA_ERR_STATE; }
+    *shard = r->shard;
     return GA_OK;
 }
 
@@ -177,7 +227,7 @@ extern "C" int ga_hub_on_chunk(ga_hub *h, const char *relay_id, const uint8_t *a
     std::lock_guard<std::mutex> lk(h->mu);
     Relay *r = find_relay(h, relay_id);
     if (!r) { set_error("ga_hub_on_chunk: relay %s is not connected", relay_id); return GA_ERR_STATE; }
-    if (!h->ctx) { set_error("ga_hub_on_chunk: this hub has no GPU context"); return GA_ERR_STATE; }
+    if (h->ctxs.empty()) { set_error("ga_hub_on_chunk: this hub has no GPU context"); return GA_ERR_STATE; }
     if (keep_stream) *keep_stream = 1;
     bool ingest = false;
     if (is_wake_word) {                                           // :962
@@ -194,7 +244,7 @@ extern "C" int ga_hub_on_chunk(ga_hub *h, const char *relay_id, const uint8_t *a
     if (ingest) {
         void *dst = nullptr;
         uint64_t off = 0;
-        int rc = ga_ring_reserve(h->ctx, nbytes, &dst, &off);
+        int rc = ga_ring_reserve(h->ctxs[r->shard], nbytes, &dst, &off);
         if (rc) return rc;
         if (nbytes) std::memcpy(dst, audio, nbytes);
         ga_msg m{};
@@ -202,7 +252,7 @@ extern "C" int ga_hub_on_chunk(ga_hub *h, const char *relay_id, const uint8_t *a
         m.flags = (is_wake_word ? GA_MSG_WAKE : 0u) | (is_end_of_speech ? GA_MSG_EOS : 0u) |
                   (r->first_chunk ? GA_MSG_FIRST : 0u);
         r->first_chunk = false;
-        h->pending.push_back(m);
+        h->pending[r->shard].push_back(m);
     }
     if (is_end_of_speech) {                                       // :1008-1041
         const bool active = r->in_active_streams && (r->status == GA_RELAY_WINNER || r->status == GA_RELAY_CONNECTED ||
@@ -212,17 +262,16 @@ extern "C" int ga_hub_on_chunk(ga_hub *h, const char *relay_id, const uint8_t *a
     return GA_OK;
 }
 
-// The batch tick: everything pushed since the last flush goes through ONE ga_submit.
-extern "C" int ga_hub_flush(ga_hub *h, uint32_t *n_msgs)
+// The batch tick: everything pushed since the last flush goes through ONE ga_submit per GPU.
+static int flush_shard(ga_hub *h, uint32_t shard, uint32_t *taken)
 {
-    if (!h) { set_error("ga_hub_flush: NULL hub"); return GA_ERR_ARG; }
-    if (!h->ctx) { set_error("ga_hub_flush: this hub has no GPU context"); return GA_ERR_STATE; }
+    ga_ctx *ctx = h->ctxs[shard];
     std::vector<ga_msg> batch;
     {
         std::lock_guard<std::mutex> lk(h->mu);   // only to take the queue: chunks keep arriving while the GPU works
-        batch.swap(h->pending);
+        batch.swap(h->pending[shard]);
     }
-    if (n_msgs) *n_msgs = static_cast<uint32_t>(batch.size());
+    *taken = static_cast<uint32_t>(batch.size());
     if (batch.empty()) return GA_OK;
     // A relay that finished an utterance and started the next one within one tick has chunks of
     // both in the queue; ga_submit wants the restart in a later batch than the old chunks, so
@@ -241,26 +290,42 @@ extern "C" int ga_hub_flush(ga_hub *h, uint32_t *n_msgs)
     size_t lo = 0;
     for (size_t hi : cuts) {
         uint64_t ticket = 0;
-        int rc = ga_submit(h->ctx, batch.data() + lo, static_cast<uint32_t>(hi - lo), &ticket);
+        int rc = ga_submit(ctx, batch.data() + lo, static_cast<uint32_t>(hi - lo), &ticket);
         if (rc) {                                // nothing of [lo, end) was queued: those chunks stay pending, in order
             std::lock_guard<std::mutex> lk(h->mu);
-            h->pending.insert(h->pending.begin(), batch.begin() + lo, batch.end());
-            if (n_msgs) *n_msgs = static_cast<uint32_t>(lo);
+            h->pending[shard].insert(h->pending[shard].begin(), batch.begin() + lo, batch.end());
+            *taken = static_cast<uint32_t>(lo);
             return rc;
         }
-        rc = ga_wait_view(h->ctx, ticket, nullptr, nullptr, nullptr, nullptr);
+        rc = ga_wait_view(ctx, ticket, nullptr, nullptr, nullptr, nullptr);
         if (rc) return rc;
         lo = hi;
     }
     return GA_OK;
 }
 
+extern "C" int ga_hub_flush(ga_hub *h, uint32_t *n_msgs)
+{
+    if (!h) { set_error("ga_hub_flush: NULL hub"); return GA_ERR_ARG; }
+    if (h->ctxs.empty()) { set_error("ga_hub_flush: this hub has no GPU context"); return GA_ERR_STATE; }
+    uint32_t total = 0;
+    int first_err = GA_OK;
+    for (uint32_t sh = 0; sh < h->ctxs.size(); sh++) {     // a failing shard does not hold the others back
+        uint32_t taken = 0;
+        const int rc = flush_shard(h, sh, &taken);
+        total += taken;
+        if (rc && !first_err) first_err = rc;
+    }
+    if (n_msgs) *n_msgs = total;
+    return first_err;
+}
+
 // performArbitration :505-587 for a set of windows at once.
 static int arbitrate_windows(ga_hub *h, const std::vector<uint64_t> &ids)
 {
     if (ids.empty()) return GA_OK;
-    if (!h->ctx) { set_error("arbitration needs a GPU context"); return GA_ERR_STATE; }
-    std::vector<uint32_t> seg(1, 0), sid, win_idx;
+    if (h->ctxs.empty()) { set_error("arbitration needs a GPU context"); return GA_ERR_STATE; }
+    std::vector<uint32_t> seg(1, 0), sid, shard, win_idx;
     std::vector<uint8_t> st_in, st_out;
     std::vector<double> scores;
     std::vector<Window *> ws;
@@ -271,6 +336,7 @@ static int arbitrate_windows(ga_hub *h, const std::vector<uint64_t> &ids)
         for (auto &rid : w.relays) {
             Relay &r = h->relays[rid];
             sid.push_back(r.slot);
+            shard.push_back(r.shard);
             st_in.push_back(static_cast<uint8_t>(r.status));
             scores.push_back(r.signal_strength);                          // untouched for skipped relays (:522-524)
         }
@@ -280,8 +346,12 @@ static int arbitrate_windows(ga_hub *h, const std::vector<uint64_t> &ids)
     if (ws.empty()) return GA_OK;
     win_idx.resize(ws.size());
     st_out.resize(sid.size());
-    int rc = ga_arbitrate(h->ctx, seg.data(), static_cast<uint32_t>(ws.size()), sid.data(), st_in.data(),
-                          win_idx.data(), scores.data(), st_out.data());
+    // one GPU: the context's own call; several: one fused launch per GPU, windows may span them
+    int rc = h->cluster
+        ? ga_cluster_arbitrate(h->cluster, seg.data(), static_cast<uint32_t>(ws.size()), shard.data(), sid.data(),
+                               st_in.data(), win_idx.data(), scores.data(), st_out.data())
+        : ga_arbitrate(h->ctxs[0], seg.data(), static_cast<uint32_t>(ws.size()), sid.data(), st_in.data(),
+                       win_idx.data(), scores.data(), st_out.data());
     if (rc) return rc;
     for (size_t k = 0; k < ws.size(); k++) {
         Window &w = *ws[k];
@@ -403,10 +473,10 @@ extern "C" int ga_hub_cleanup_relay(ga_hub *h, const char *relay_id)
     std::lock_guard<std::mutex> lk(h->mu);
     auto it = h->relays.find(relay_id);
     if (it == h->relays.end()) return GA_OK;                 // nonexistent relay: not an error (:916-923, test :316)
-    const uint32_t slot = it->second.slot;
+    const uint32_t slot = it->second.slot, shard = it->second.shard;
     h->relays.erase(it);
-    h->free_slots.push_back(slot);
-    return h->ctx ? ga_stream_reset(h->ctx, slot) : GA_OK;
+    h->free_slots[shard].push_back(slot);
+    return h->ctxs.empty() ? GA_OK : ga_stream_reset(h->ctxs[shard], slot);
 }
 
 extern "C" int ga_hub_active_streams(ga_hub *h, uint32_t *n)
@@ -443,4 +513,20 @@ extern "C" int ga_fetch_wav(ga_ctx *ctx, uint32_t stream_id, uint32_t sample_rat
     std::memcpy(out + 36, "data", 4);  le32(out + 40, static_cast<uint32_t>(data_size));  // :387-388
     if (n == 0) return GA_OK;
     return ga_fetch_samples(ctx, stream_id, 0, n, reinterpret_cast<float *>(out + 44));
+}
+
+// The winner's audio as the STT request body, from whichever GPU holds it.
+extern "C" int ga_hub_fetch_wav(ga_hub *h, const char *relay_id, uint32_t sample_rate, uint8_t *out, size_t cap, size_t *n_bytes)
+{
+    if (!h || !relay_id) { set_error("ga_hub_fetch_wav: bad argument"); return GA_ERR_ARG; }
+    ga_ctx *ctx = nullptr;
+    uint32_t slot = 0;
+    {
+        std::lock_guard<std::mutex> lk(h->mu);
+        Relay *r = find_relay(h, relay_id);
+        if (!r) { set_error("ga_hub_fetch_wav: unknown relay %s", relay_id); return GA_ERR_STATE; }
+        if (h->ctxs.empty()) { set_error("ga_hub_fetch_wav: this hub has no GPU context"); return GA_ERR_STATE; }
+        ctx = h->ctxs[r->shard]; slot = r->slot;
+    }
+    return ga_fetch_wav(ctx, slot, sample_rate, out, cap, n_bytes);
 }

@@ -122,3 +122,60 @@ def test_spanning_windows_across_gpus_match_the_oracle():
     finally:
         for c in ctxs:
             c.close()
+
+
+# ---------------------------------------------------------------- the hub over several GPUs
+def test_hub_over_two_gpus_spanning_windows_and_winner_audio():
+    """The StreamAudio flow (audio_service.go:939-1041) with relays on two GPUs: groups homed by
+    group % nGPU, two relays of every group forced onto the other GPU so that every window spans;
+    wake-word chunks, window close by the timer, winners, cancelled relays, and the winner's WAV
+    (stt_client.go:365-398) from whichever GPU holds it — all against the oracle."""
+    if n_devices() < 2:
+        pytest.skip("needs 2 GPUs")
+    from loqa_hub_b200 import synth
+    from loqa_hub_b200.audio_service import AudioService, RelayStatusCancelled, RelayStatusWinner
+    MS = 1000
+    ctxs = [make_ctx(d, streams=64) for d in range(2)]
+    try:
+        with api.Cluster(ctxs) as cl:
+            svc = AudioService(cl, max_streams=64, window_duration_us=100 * MS)
+            n_groups, n_relays, wake_msgs, ms = 6, 4, 5, 320
+            pcm, name = {}, lambda g, r: "g%d-relay%d" % (g, r)
+            for g in range(n_groups):
+                for r in range(n_relays):
+                    if r < 2:
+                        svc.connect(name(g, r), group=g)                     # home shard g % 2
+                    else:
+                        svc.connect_on(name(g, r), g, (g + 1) % 2)           # the other GPU
+                    assert svc.relay_shard(name(g, r)) == (g % 2 if r < 2 else (g + 1) % 2)
+                    pcm[g, r] = synth.relay_view(g, r, wake_msgs * ms + 3 * ms).astype("<i2")
+            # the quietest relay speaks first, the loudest (relay 0) joins last: order must not matter
+            for m in range(wake_msgs):
+                for g in range(n_groups):
+                    for r in reversed(range(n_relays)):
+                        assert svc.on_chunk(name(g, r), pcm[g, r][m * ms:(m + 1) * ms].tobytes(), True, False, (10 * m + n_relays - 1 - r) * MS)
+            assert svc.flush() == n_groups * n_relays * wake_msgs
+            assert svc.poll(now_us=50 * MS) == 0
+            assert svc.poll(now_us=200 * MS) == n_groups
+            for g in range(n_groups):
+                sig = [ora.bytes_to_float32(pcm[g, r][:wake_msgs * ms].tobytes())[0] for r in reversed(range(n_relays))]
+                w, sc, _ = ora.arbitrate(sig)
+                winner = name(g, n_relays - 1 - w)
+                assert winner == name(g, 0)                                   # relay 0 has gain 1.0
+                for k, r in enumerate(reversed(range(n_relays))):
+                    info = svc.relay(name(g, r))
+                    assert info.signal_strength == sc[k]
+                    assert info.status == (RelayStatusWinner if name(g, r) == winner else RelayStatusCancelled)
+                assert svc.arbitration_window(g) is None
+            # speech for the winners only (cancelled relays' handlers have returned), then their WAVs
+            for m in range(wake_msgs, wake_msgs + 3):
+                for g in range(n_groups):
+                    svc.on_chunk(name(g, 0), pcm[g, 0][m * ms:(m + 1) * ms].tobytes(), False, m == wake_msgs + 2, 300 * MS)
+            svc.flush()
+            for g in range(n_groups):
+                full = ora.bytes_to_float32(pcm[g, 0].tobytes())[0]
+                assert svc.fetch_wav(name(g, 0)) == ora.float32_to_wav(full, 16000)
+            svc.close()
+    finally:
+        for c in ctxs:
+            c.close()
