@@ -262,61 +262,74 @@ extern "C" int ga_hub_on_chunk(ga_hub *h, const char *relay_id, const uint8_t *a
     return GA_OK;
 }
 
-// The batch tick: everything pushed since the last flush goes through ONE ga_submit per GPU.
-static int flush_shard(ga_hub *h, uint32_t shard, uint32_t *taken)
-{
-    ga_ctx *ctx = h->ctxs[shard];
-    std::vector<ga_msg> batch;
-    {
-        std::lock_guard<std::mutex> lk(h->mu);   // only to take the queue: chunks keep arriving while the GPU works
-        batch.swap(h->pending[shard]);
-    }
-    *taken = static_cast<uint32_t>(batch.size());
-    if (batch.empty()) return GA_OK;
-    // A relay that finished an utterance and started the next one within one tick has chunks of
-    // both in the queue; ga_submit wants the restart in a later batch than the old chunks, so
-    // cut the queue there (rare: normally one submit).
-    std::vector<size_t> cuts;
-    bool any_first = false;
-    for (size_t k = 1; k < batch.size() && !any_first; k++) any_first = (batch[k].flags & GA_MSG_FIRST) != 0;
-    if (any_first) {
-        std::unordered_set<uint32_t> seen;
-        for (size_t k = 0; k < batch.size(); k++) {
-            if ((batch[k].flags & GA_MSG_FIRST) && seen.count(batch[k].stream_id)) { cuts.push_back(k); seen.clear(); }
-            seen.insert(batch[k].stream_id);
-        }
-    }
-    cuts.push_back(batch.size());
-    size_t lo = 0;
-    for (size_t hi : cuts) {
-        uint64_t ticket = 0;
-        int rc = ga_submit(ctx, batch.data() + lo, static_cast<uint32_t>(hi - lo), &ticket);
-        if (rc) {                                // nothing of [lo, end) was queued: those chunks stay pending, in order
-            std::lock_guard<std::mutex> lk(h->mu);
-            h->pending[shard].insert(h->pending[shard].begin(), batch.begin() + lo, batch.end());
-            *taken = static_cast<uint32_t>(lo);
-            return rc;
-        }
-        rc = ga_wait_view(ctx, ticket, nullptr, nullptr, nullptr, nullptr);
-        if (rc) return rc;
-        lo = hi;
-    }
-    return GA_OK;
-}
-
+// The batch tick: everything pushed since the last flush goes through ONE ga_submit per GPU, all
+// GPUs working at the same time.
 extern "C" int ga_hub_flush(ga_hub *h, uint32_t *n_msgs)
 {
     if (!h) { set_error("ga_hub_flush: NULL hub"); return GA_ERR_ARG; }
     if (h->ctxs.empty()) { set_error("ga_hub_flush: this hub has no GPU context"); return GA_ERR_STATE; }
-    uint32_t total = 0;
-    int first_err = GA_OK;
-    for (uint32_t sh = 0; sh < h->ctxs.size(); sh++) {     // a failing shard does not hold the others back
-        uint32_t taken = 0;
-        const int rc = flush_shard(h, sh, &taken);
-        total += taken;
-        if (rc && !first_err) first_err = rc;
+    struct Work {
+        std::vector<ga_msg> batch;
+        std::vector<size_t> cuts;     // ends of the sub-batches
+        size_t next = 0, lo = 0;      // next sub-batch to submit, first message not yet submitted
+        uint64_t ticket = 0;
+        bool inflight = false, done = false;
+    };
+    const uint32_t n_sh = static_cast<uint32_t>(h->ctxs.size());
+    std::vector<Work> work(n_sh);
+    {
+        std::lock_guard<std::mutex> lk(h->mu);   // only to take the queues: chunks keep arriving while the GPUs work
+        for (uint32_t sh = 0; sh < n_sh; sh++) work[sh].batch.swap(h->pending[sh]);
     }
-    if (n_msgs) *n_msgs = total;
+    uint32_t total = 0;
+    for (auto &w : work) {
+        total += static_cast<uint32_t>(w.batch.size());
+        w.done = w.batch.empty();
+        // A relay that finished an utterance and started the next one within one tick has chunks
+        // of both in the queue; ga_submit wants the restart in a later batch than the old chunks,
+        // so the queue is cut there (rare: normally one submit per GPU).
+        bool any_first = false;
+        for (size_t k = 1; k < w.batch.size() && !any_first; k++) any_first = (w.batch[k].flags & GA_MSG_FIRST) != 0;
+        if (any_first) {
+            std::unordered_set<uint32_t> seen;
+            for (size_t k = 0; k < w.batch.size(); k++) {
+                if ((w.batch[k].flags & GA_MSG_FIRST) && seen.count(w.batch[k].stream_id)) { w.cuts.push_back(k); seen.clear(); }
+                seen.insert(w.batch[k].stream_id);
+            }
+        }
+        w.cuts.push_back(w.batch.size());
+    }
+    int first_err = GA_OK;
+    uint32_t lost = 0;
+    for (bool busy = true; busy;) {
+        busy = false;
+        for (uint32_t sh = 0; sh < n_sh; sh++) {            // round k: the k-th sub-batch of every GPU
+            Work &w = work[sh];
+            if (w.done) continue;
+            const size_t hi = w.cuts[w.next];
+            const int rc = ga_submit(h->ctxs[sh], w.batch.data() + w.lo, static_cast<uint32_t>(hi - w.lo), &w.ticket);
+            if (rc) {                                       // nothing of [lo, end) was queued: it stays pending, in order
+                std::lock_guard<std::mutex> lk(h->mu);
+                h->pending[sh].insert(h->pending[sh].begin(), w.batch.begin() + w.lo, w.batch.end());
+                lost += static_cast<uint32_t>(w.batch.size() - w.lo);
+                w.done = true;
+                if (!first_err) first_err = rc;             // a failing GPU does not hold the others back
+                continue;
+            }
+            w.inflight = true;
+            w.lo = hi;
+            w.next++;
+        }
+        for (uint32_t sh = 0; sh < n_sh; sh++) {
+            Work &w = work[sh];
+            if (!w.inflight) continue;
+            w.inflight = false;
+            const int rc = ga_wait_view(h->ctxs[sh], w.ticket, nullptr, nullptr, nullptr, nullptr);
+            if (rc) { w.done = true; if (!first_err) first_err = rc; continue; }
+            if (w.next == w.cuts.size()) w.done = true; else busy = true;
+        }
+    }
+    if (n_msgs) *n_msgs = total - lost;
     return first_err;
 }
 
