@@ -95,7 +95,7 @@ def test_more_remote_relays_than_the_cluster_was_sized_for():
 
 
 def test_spanning_windows_across_gpus_match_the_oracle():
-    n = min(n_devices(), 4)
+    n = min(n_devices(), 8)
     if n < 2:
         pytest.skip("needs 2 GPUs")
     rng = np.random.default_rng(3)
