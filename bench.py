@@ -404,7 +404,7 @@ def main():
 
     # ---- end to end through the host C ABI
     e2e = None
-    if not args.no_e2e and not fmt48:        # cfg4 would need a 7.9 GB pinned ring: device-resident numbers only
+    if not args.no_e2e:
         with ClockSampler(local_rank) as clk2:
             e2e = run_e2e(args, w, plan, pcm, arbitration, d_winner, world, rank, local_rank, dev)
         clk.lines += clk2.lines
@@ -484,23 +484,32 @@ def run_e2e(args, w, plan, pcm, arbitration, d_winner, world, rank, local_rank, 
     while M % tps:
         tps -= 1
     sub_msgs, n_sub = S * tps, M // tps
-    sub_bytes = sub_msgs * ms * 2
-    ring_bytes = sub_bytes * n_sub
+    fmt48 = bool(w.get("stereo48"))
+    chunk = ms * 12 if fmt48 else ms * 2
+    sub_bytes = sub_msgs * chunk
+    # mono: the ring holds the whole step.  48 kHz stereo (7.9 GB per step): a ring of 5 submits that the
+    # step goes round five times — submits 5.. re-send the bytes of submits 0..4 (the wake-word part
+    # that arbitration reads is in submits 0-1 and is the real data)
+    n_host = n_sub if not fmt48 else min(n_sub, 5)
+    while n_sub % n_host:
+        n_host -= 1
+    ring_bytes = sub_bytes * n_host
     ctx = api.Context(device=local_rank, max_streams=S, max_batch_msgs=sub_msgs, max_inflight=4,
                       ring_bytes=ring_bytes, arena_samples=M * ms, wake_samples_max=wake * ms,
                       mode=L.DO_ALL, want_frames=False,
+                      input_format=L.FMT_STEREO48K if fmt48 else L.FMT_MONO16K,
                       staging=L.STAGING_AUTO if args.staging == "tmap" else L.STAGING_BULK)
     import ctypes as C
     arena_ptr = C.c_void_p()
     L.check(L.load().ga_device_arena(ctx._h, C.byref(arena_ptr)))
-    host_pcm = pcm.cpu().numpy().view(np.uint8)
+    host_pcm = pcm[: ring_bytes // 2].cpu().numpy().view(np.uint8)
     k = np.arange(sub_msgs, dtype=np.uint64)
-    rel = k * (ms * 2)
+    rel = k * chunk
     msgs = []
     for j in range(n_sub):
         m_idx = j * tps + k // S
         mm = np.zeros(sub_msgs, dtype=L.MSG_DTYPE)
-        mm["nbytes"] = ms * 2
+        mm["nbytes"] = chunk
         mm["stream_id"] = (k % S).astype(np.uint32)
         mm["flags"] = (np.where(m_idx < wake, L.MSG_WAKE, 0) | np.where(m_idx == 0, L.MSG_FIRST, 0) |
                        np.where(m_idx == M - 1, L.MSG_EOS, 0)).astype(np.uint32)
@@ -510,11 +519,11 @@ def run_e2e(args, w, plan, pcm, arbitration, d_winner, world, rank, local_rank, 
 
     def wait(t):       # zero-copy: the result records stay in the C-owned pinned buffer
         L.check(lib.ga_wait_view(ctx._h, t, C.byref(res_p), None, C.byref(res_n), None))
-    ticks = args.submit == "ticks"
+    ticks = args.submit == "ticks" and not fmt48       # ga_submit_ticks is for mono contexts
     ids = np.arange(S, dtype=np.uint32)
     tick_flags = [np.ascontiguousarray(mm["flags"].astype(np.uint8)) for mm in msgs]
     # per-message descriptors (32 B each) or, for ga_submit_ticks, 1 flag byte per message + 12 B per stream
-    h2d = ring_bytes + (n_sub * (sub_msgs + 12 * S) if ticks else sub_msgs * n_sub * 32)
+    h2d = sub_bytes * n_sub + (n_sub * (sub_msgs + 12 * S) if ticks else sub_msgs * n_sub * (96 if fmt48 else 32))
     d2h = sub_msgs * n_sub * 64 + plan.n_windows * 4
 
     def one_step(fill):
@@ -522,7 +531,7 @@ def run_e2e(args, w, plan, pcm, arbitration, d_winner, world, rank, local_rank, 
         for j in range(n_sub):
             view, off = ctx.reserve(sub_bytes)
             if fill:                                    # first pass only: the relays' bytes land in the ring
-                view[:sub_bytes] = host_pcm[j * sub_bytes:(j + 1) * sub_bytes]
+                view[:sub_bytes] = host_pcm[(j % n_host) * sub_bytes:(j % n_host + 1) * sub_bytes]
             t = C.c_uint64()
             if ticks:
                 L.check(lib.ga_submit_ticks(ctx._h, off, tps, S, ms * 2, L.ptr(ids), L.ptr(tick_flags[j]), C.byref(t)))
@@ -560,7 +569,8 @@ def run_e2e(args, w, plan, pcm, arbitration, d_winner, world, rank, local_rank, 
         raise SystemExit("bench: e2e arbitration winners are wrong on rank %d" % rank)
     # spot check one digest of the last sub-batch against hashlib (not the oracle)
     import hashlib
-    last = host_pcm[(n_sub - 1) * sub_bytes:(n_sub - 1) * sub_bytes + ms * 2].tobytes()
+    jl = (n_sub - 1) % n_host
+    last = host_pcm[jl * sub_bytes:jl * sub_bytes + chunk].tobytes()
     res_last = np.ctypeslib.as_array(C.cast(res_p, C.POINTER(C.c_uint8)), shape=(64,))
     if res_last[:32].tobytes() != hashlib.sha256(last).digest():
         raise SystemExit("bench: e2e digest mismatch on rank %d" % rank)

@@ -529,7 +529,12 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
             // fills the statistics of the resampled samples into the same records
             GA_CUDA_TRY(cudaMemcpyAsync(slot->d_rdesc, slot->h_rdesc, sizeof(ga_rdesc) * n, cudaMemcpyHostToDevice, s));
             if (ctx->cfg.mode & GA_DO_SHA256) {
-                rc = ga_k_ingest(ctx->d_ring, slot->d_desc, n, nullptr, slot->d_res, nullptr, GA_DO_SHA256, ctx->cfg.vad_threshold, s);
+                // equal-sized chunks back to back (a tick of 20 ms chunks): tensor-map staging here too
+                if (uniform && msgs[0].nbytes && ctx->cfg.staging != GA_STAGING_BULK)
+                    rc = ga_k_ingest_uniform(ctx->d_ring, slot->d_desc, n, phys0, msgs[0].nbytes, ustride, nullptr, slot->d_res,
+                                             nullptr, GA_DO_SHA256, ctx->cfg.vad_threshold, s);
+                else
+                    rc = ga_k_ingest(ctx->d_ring, slot->d_desc, n, nullptr, slot->d_res, nullptr, GA_DO_SHA256, ctx->cfg.vad_threshold, s);
                 if (rc) return rc;
             } else {
                 GA_CUDA_TRY(cudaMemsetAsync(slot->d_res, 0, sizeof(ga_result) * n, s));
