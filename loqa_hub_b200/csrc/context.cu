@@ -1321,7 +1321,8 @@ struct ClusterShard {
     int dev = 0;
     cudaStream_t stream = nullptr;
     uint8_t *region = nullptr;            // inbox[2][cap] f64 | flags[n_shards] u64 | counter, error u32
-    uint8_t *scratch = nullptr;           // grow-only device tables
+    uint8_t *scratch = nullptr;           // grow-only device tables ...
+    uint8_t *h_stage = nullptr;           // ... and their pinned host mirror: one copy in, one copy out per call
     size_t scratch_bytes = 0;
     // per-call host tables
     std::vector<uint64_t> off, guest_dst, notify, wait;
@@ -1335,7 +1336,7 @@ struct ClusterShard {
     std::vector<uint8_t> st_out;
     uint32_t err = 0;
     bool launched = false;
-    size_t o_win = 0, o_sc = 0, o_so = 0;
+    size_t o_win = 0, o_sc = 0, o_so = 0, o_err = 0;
 };
 
 }  // namespace ga
@@ -1356,6 +1357,7 @@ extern "C" void ga_cluster_destroy(ga_cluster *cl)
         if (s.stream) { cudaStreamSynchronize(s.stream); cudaStreamDestroy(s.stream); }
         if (s.region) cudaFree(s.region);
         if (s.scratch) cudaFree(s.scratch);
+        if (s.h_stage) cudaFreeHost(s.h_stage);
     }
     delete cl;
 }
@@ -1446,9 +1448,12 @@ extern "C" int ga_cluster_arbitrate(ga_cluster *cl, const uint32_t *seg_offsets,
         s.incoming.clear(); s.guest_dst.clear(); s.notify.clear(); s.wait.clear(); s.route_dst.clear();
         s.n_home = s.n_guests = 0; s.err = 0;
     }
+    // the streams' wake-word cursors are read under the contexts' locks, taken once each, in shard order
+    std::vector<std::unique_lock<std::mutex>> ctx_locks;
+    ctx_locks.reserve(n_sh);
+    for (auto &s : cl->shards) ctx_locks.emplace_back(s.ctx->mu);
     auto wake_of = [&](uint32_t shard, uint32_t sid, uint64_t &off, uint32_t &cnt) {
         ga_ctx *c = cl->shards[shard].ctx;
-        std::lock_guard<std::mutex> g(c->mu);
         off = static_cast<uint64_t>(sid) * c->cfg.arena_samples;
         cnt = static_cast<uint32_t>(c->streams[sid].wake_n);
     };
@@ -1499,6 +1504,8 @@ extern "C" int ga_cluster_arbitrate(ga_cluster *cl, const uint32_t *seg_offsets,
                 cl->shards[b].wait.push_back(reinterpret_cast<uint64_t>(cl->shards[b].region) + cl->flags_off + 8ull * a);
             }
 
+    ctx_locks.clear();
+
     // ---- one launch per GPU; nothing is waited for until all of them are queued
     const uint64_t epoch = ++cl->epoch;
     auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
@@ -1509,23 +1516,35 @@ extern "C" int ga_cluster_arbitrate(ga_cluster *cl, const uint32_t *seg_offsets,
         if (n_all == 0 && s.notify.empty()) continue;
         auto step = [&]() -> int {
             GA_CUDA_TRY(cudaSetDevice(s.dev));
-            const size_t o_off = 0, o_cnt = o_off + up(8 * n_all), o_st = o_cnt + up(4 * n_all), o_sc = o_st + up(n_all),
-                         o_seg = o_sc + up(8 * n_all), o_win = o_seg + up(4 * (nw + 1)), o_so = o_win + up(4 * nw),
-                         o_gd = o_so + up(s.n_home), o_no = o_gd + up(8 * s.guest_dst.size()), o_wa = o_no + up(8 * s.notify.size()),
-                         o_rd = o_wa + up(8 * s.wait.size()), need = o_rd + up(4 * s.route_dst.size()) + 256;
+            // inputs | error word, scores (in and out) | winners, statuses (out): the tables go up in ONE
+            // copy from the pinned mirror and the results come back in ONE
+            const size_t o_off = 0, o_cnt = o_off + up(8 * n_all), o_st = o_cnt + up(4 * n_all), o_seg = o_st + up(n_all),
+                         o_gd = o_seg + up(4 * (nw + 1)), o_no = o_gd + up(8 * s.guest_dst.size()),
+                         o_wa = o_no + up(8 * s.notify.size()), o_rd = o_wa + up(8 * s.wait.size()),
+                         o_err = o_rd + up(4 * s.route_dst.size()), o_sc = o_err + 256, o_win = o_sc + up(8 * n_all),
+                         o_so = o_win + up(4 * nw), need = o_so + up(s.n_home) + 256;
             if (need > s.scratch_bytes) {
                 GA_CUDA_TRY(cudaStreamSynchronize(s.stream));
                 if (s.scratch) cudaFree(s.scratch);
-                s.scratch = nullptr; s.scratch_bytes = 0;
-                cudaError_t e = cudaMalloc(reinterpret_cast<void **>(&s.scratch), need + need / 2);
-                if (e != cudaSuccess) { cudaGetLastError(); set_error("ga_cluster_arbitrate: cudaMalloc failed: %s", cudaGetErrorString(e)); return GA_ERR_NOMEM; }
-                s.scratch_bytes = need + need / 2;
+                if (s.h_stage) cudaFreeHost(s.h_stage);
+                s.scratch = nullptr; s.h_stage = nullptr; s.scratch_bytes = 0;
+                const size_t want = need + need / 2;
+                cudaError_t e = cudaMalloc(reinterpret_cast<void **>(&s.scratch), want);
+                if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void **>(&s.h_stage), want, cudaHostAllocDefault);
+                if (e != cudaSuccess) {
+                    cudaGetLastError();
+                    if (s.scratch) { cudaFree(s.scratch); s.scratch = nullptr; }
+                    set_error("ga_cluster_arbitrate: allocating %zu bytes of tables failed: %s", want, cudaGetErrorString(e));
+                    return GA_ERR_NOMEM;
+                }
+                s.scratch_bytes = want;
             }
             uint8_t *b = s.scratch;
             auto put = [&](size_t o, const void *src, size_t bytes) -> int {
-                if (bytes) GA_CUDA_TRY(cudaMemcpyAsync(b + o, src, bytes, cudaMemcpyHostToDevice, s.stream));
+                if (bytes) std::memcpy(s.h_stage + o, src, bytes);
                 return GA_OK;
             };
+            std::memset(s.h_stage + o_err, 0, 4);
             {   // the wake-word buffers must be complete: wait for every ticket of this context in flight
                 std::lock_guard<std::mutex> g(s.ctx->mu);
                 int r = join_inflight(s.ctx, s.stream);
@@ -1538,6 +1557,7 @@ extern "C" int ga_cluster_arbitrate(ga_cluster *cl, const uint32_t *seg_offsets,
                 (r = put(o_no, s.notify.data(), 8 * s.notify.size())) || (r = put(o_wa, s.wait.data(), 8 * s.wait.size())) ||
                 (r = put(o_rd, s.route_dst.data(), 4 * s.route_dst.size())))
                 return r;
+            GA_CUDA_TRY(cudaMemcpyAsync(b, s.h_stage, o_win, cudaMemcpyHostToDevice, s.stream));
             ga_p2p_args a;
             std::memset(&a, 0, sizeof a);
             a.d_samples = s.ctx->d_arena;
@@ -1549,7 +1569,7 @@ extern "C" int ga_cluster_arbitrate(ga_cluster *cl, const uint32_t *seg_offsets,
             a.d_wait = reinterpret_cast<uint64_t *>(b + o_wa); a.d_inbox = reinterpret_cast<double *>(s.region);
             a.d_route_dst = reinterpret_cast<uint32_t *>(b + o_rd);
             a.d_counter = reinterpret_cast<uint32_t *>(s.region + cl->ctl_off);
-            a.d_error = reinterpret_cast<uint32_t *>(s.region + cl->ctl_off + 4);
+            a.d_error = reinterpret_cast<uint32_t *>(b + o_err);
             a.inbox_parity_stride = cl->parity_stride;
             a.epoch = epoch;
             a.timeout_cycles = 4'000'000'000ll;          // ~2 s: a peer that never launched must not hang this GPU
@@ -1558,10 +1578,10 @@ extern "C" int ga_cluster_arbitrate(ga_cluster *cl, const uint32_t *seg_offsets,
             a.n_in = static_cast<uint32_t>(s.route_dst.size());
             r = ga_k_arbitrate_p2p(&a, s.stream);
             if (r) return r;
-            // results are fetched only after EVERY shard's kernel is queued: a copy into pageable
-            // memory blocks the host until this shard's kernel is done, and that kernel may be
-            // waiting for a shard that is launched later in this loop
-            s.launched = true; s.o_win = o_win; s.o_sc = o_sc; s.o_so = o_so;
+            // into PINNED memory, so this does not block the host: the kernel may be waiting for a
+            // shard that is only launched later in this loop
+            GA_CUDA_TRY(cudaMemcpyAsync(s.h_stage + o_err, b + o_err, need - 256 - o_err, cudaMemcpyDeviceToHost, s.stream));
+            s.launched = true; s.o_win = o_win; s.o_sc = o_sc; s.o_so = o_so; s.o_err = o_err;
             return GA_OK;
         };
         rc = step();
@@ -1573,19 +1593,24 @@ extern "C" int ga_cluster_arbitrate(ga_cluster *cl, const uint32_t *seg_offsets,
         s.launched = false;
         cudaSetDevice(s.dev);
         const size_t nw = s.windows.size();
+        cudaError_t e = cudaStreamSynchronize(s.stream);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            if (rc == GA_OK) { set_error("ga_cluster_arbitrate: device %d: %s", s.dev, cudaGetErrorString(e)); rc = GA_ERR_CUDA; }
+            continue;
+        }
         s.win_out.resize(nw); s.st_out.resize(s.n_home);
-        cudaError_t e = cudaSuccess;
-        if (nw) e = cudaMemcpyAsync(s.win_out.data(), s.scratch + s.o_win, 4 * nw, cudaMemcpyDeviceToHost, s.stream);
-        if (e == cudaSuccess && s.n_home) e = cudaMemcpyAsync(s.sc.data(), s.scratch + s.o_sc, 8ull * s.n_home, cudaMemcpyDeviceToHost, s.stream);
-        if (e == cudaSuccess && s.n_home) e = cudaMemcpyAsync(s.st_out.data(), s.scratch + s.o_so, s.n_home, cudaMemcpyDeviceToHost, s.stream);
-        if (e == cudaSuccess) e = cudaMemcpyAsync(&s.err, s.region + cl->ctl_off + 4, 4, cudaMemcpyDeviceToHost, s.stream);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(s.stream);
-        if (e != cudaSuccess && rc == GA_OK) { cudaGetLastError(); set_error("ga_cluster_arbitrate: device %d: %s", s.dev, cudaGetErrorString(e)); rc = GA_ERR_CUDA; }
+        std::memcpy(&s.err, s.h_stage + s.o_err, 4);
+        if (nw) std::memcpy(s.win_out.data(), s.h_stage + s.o_win, 4 * nw);
+        if (s.n_home) {
+            std::memcpy(s.sc.data(), s.h_stage + s.o_sc, 8ull * s.n_home);
+            std::memcpy(s.st_out.data(), s.h_stage + s.o_so, s.n_home);
+        }
         if (s.err && rc == GA_OK) {
             set_error("ga_cluster_arbitrate: shard %u timed out waiting for a peer's scores", i);
             rc = GA_ERR_COMM;
         }
-        if (s.err) { cudaMemsetAsync(s.region + cl->ctl_off + 4, 0, 4, s.stream); cudaStreamSynchronize(s.stream); s.err = 0; }
+        s.err = 0;
     }
     if (rc) return rc;
     for (auto &s : cl->shards) {
