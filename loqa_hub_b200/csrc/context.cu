@@ -90,6 +90,7 @@ struct ga_ctx {
     uint64_t fence_ticket = 0;                 // tickets up to this one must finish before the next batch's kernels
                                                // start: a restarted stream reuses arena space they may still write
     uint8_t *d_arb = nullptr;                  // grow-only device scratch of ga_arbitrate (no per-call cudaMalloc)
+    uint8_t *h_arb = nullptr;                  // its pinned host mirror: one copy up, one copy down per call
     size_t arb_bytes = 0;
     std::mutex mu;   // guards submit/wait/arbitrate bookkeeping (not the ring reserve path)
     // scratch for ga_arbitrate
@@ -133,6 +134,7 @@ static void destroy(ga_ctx *c)
     if (c->d_hist) cudaFree(c->d_hist);
     if (c->d_sha) cudaFree(c->d_sha);
     if (c->d_arb) cudaFree(c->d_arb);
+    if (c->h_arb) cudaFreeHost(c->h_arb);
     delete c;
 }
 
@@ -177,6 +179,8 @@ static_assert(sizeof(ga_msg) == 24, "ga_msg layout");
 static_assert(sizeof(ga_rdesc) == 64, "ga_rdesc layout");
 static_assert(sizeof(ga_config) == 64, "ga_config layout");
 static_assert(sizeof(ga_sha_state) == 128, "ga_sha_state layout");
+
+static int arb_reserve(ga_ctx *ctx, size_t need);
 
 extern "C" int ga_init(const ga_config *cfg, ga_ctx **out)
 {
@@ -271,6 +275,7 @@ extern "C" int ga_init(const ga_config *cfg, ga_ctx **out)
         catch (...) { set_error("ga_init: out of host memory"); destroy(c); return GA_ERR_NOMEM; }
     }
     GA_ALLOC_TRY(cudaStreamCreateWithFlags(&c->aux, cudaStreamNonBlocking));
+    if ((cfg->mode & GA_DO_CONVERT) && arb_reserve(c, 26ull * cfg->max_streams + 4096) != GA_OK) { destroy(c); return GA_ERR_NOMEM; }
     *out = c;
     return GA_OK;
 }
@@ -976,6 +981,28 @@ struct DevBuf {   // RAII for the transient device arrays of the host-array entr
 };
 }  // namespace
 
+// Tables of ga_arbitrate: grow-only, device + pinned mirror.  ga_init sizes them for every stream
+// contending in windows of one, so a hub never allocates at window close.
+static int arb_reserve(ga_ctx *ctx, size_t need)
+{
+    if (need <= ctx->arb_bytes) return GA_OK;
+    if (ctx->aux) GA_CUDA_TRY(cudaStreamSynchronize(ctx->aux));
+    if (ctx->d_arb) cudaFree(ctx->d_arb);
+    if (ctx->h_arb) cudaFreeHost(ctx->h_arb);
+    ctx->d_arb = nullptr; ctx->h_arb = nullptr; ctx->arb_bytes = 0;
+    const size_t want = need + need / 2;
+    cudaError_t e = cudaMalloc(reinterpret_cast<void **>(&ctx->d_arb), want);
+    if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void **>(&ctx->h_arb), want, cudaHostAllocDefault);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        if (ctx->d_arb) { cudaFree(ctx->d_arb); ctx->d_arb = nullptr; }
+        set_error("ga_arbitrate: allocating %zu bytes of tables failed: %s", want, cudaGetErrorString(e));
+        return GA_ERR_NOMEM;
+    }
+    ctx->arb_bytes = want;
+    return GA_OK;
+}
+
 extern "C" int ga_arbitrate(ga_ctx *ctx, const uint32_t *seg_offsets, uint32_t n_windows,
                             const uint32_t *stream_ids, const uint8_t *status_in,
                             uint32_t *winner_idx, double *scores, uint8_t *status_out)
@@ -991,30 +1018,30 @@ extern "C" int ga_arbitrate(ga_ctx *ctx, const uint32_t *seg_offsets, uint32_t n
     std::lock_guard<std::mutex> lk(ctx->mu);
     int rc = set_device(ctx);
     if (rc) return rc;
-    std::vector<uint64_t> off(n_members);
-    std::vector<uint32_t> cnt(n_members);
-    for (uint32_t m = 0; m < n_members; m++) {
-        if (stream_ids[m] >= ctx->cfg.max_streams) { set_error("ga_arbitrate: member %u: stream_id out of range", m); return GA_ERR_ARG; }
-        off[m] = static_cast<uint64_t>(stream_ids[m]) * ctx->cfg.arena_samples;
-        cnt[m] = static_cast<uint32_t>(ctx->streams[stream_ids[m]].wake_n);
-    }
-    // device arrays carved from one grow-only scratch allocation owned by the context
+    // device arrays carved from one grow-only scratch allocation owned by the context, filled
+    // through a pinned host mirror: inputs | scores (in and out) | winners, statuses (out)
     auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
     const size_t o_off = 0, o_cnt = o_off + up(8ull * n_members), o_st = o_cnt + up(4ull * n_members),
                  o_seg = o_st + up(n_members), o_sc = o_seg + up(4ull * (n_windows + 1)),
                  o_win = o_sc + up(8ull * n_members), o_so = o_win + up(4ull * n_windows),
-                 need = o_so + up(n_members) + 256;
+                 end = o_so + up(n_members), need = end + 256;
     cudaStream_t s = ctx->aux;
-    if (need > ctx->arb_bytes) {
-        GA_CUDA_TRY(cudaStreamSynchronize(s));
-        if (ctx->d_arb) cudaFree(ctx->d_arb);
-        ctx->d_arb = nullptr; ctx->arb_bytes = 0;
-        const size_t want = need + need / 2;
-        cudaError_t e = cudaMalloc(reinterpret_cast<void **>(&ctx->d_arb), want);
-        if (e != cudaSuccess) { cudaGetLastError(); set_error("ga_arbitrate: cudaMalloc(%zu) failed: %s", want, cudaGetErrorString(e)); return GA_ERR_NOMEM; }
-        ctx->arb_bytes = want;
+    rc = arb_reserve(ctx, need);
+    if (rc) return rc;
+    uint8_t *b = ctx->d_arb, *hb = ctx->h_arb;
+    uint64_t *h_off = reinterpret_cast<uint64_t *>(hb + o_off);
+    uint32_t *h_cnt = reinterpret_cast<uint32_t *>(hb + o_cnt);
+    for (uint32_t m = 0; m < n_members; m++) {
+        if (stream_ids[m] >= ctx->cfg.max_streams) { set_error("ga_arbitrate: member %u: stream_id out of range", m); return GA_ERR_ARG; }
+        h_off[m] = static_cast<uint64_t>(stream_ids[m]) * ctx->cfg.arena_samples;
+        h_cnt[m] = static_cast<uint32_t>(ctx->streams[stream_ids[m]].wake_n);
     }
-    uint8_t *b = ctx->d_arb;
+    if (n_members) {
+        std::memcpy(hb + o_st, status_in, n_members);
+        // scores of skipped relays stay what the caller passed in (audio_service.go:522-524)
+        std::memcpy(hb + o_sc, scores, 8ull * n_members);
+    }
+    std::memcpy(hb + o_seg, seg_offsets, 4ull * (n_windows + 1));
     uint64_t *d_off = reinterpret_cast<uint64_t *>(b + o_off);
     uint32_t *d_cnt = reinterpret_cast<uint32_t *>(b + o_cnt), *d_seg = reinterpret_cast<uint32_t *>(b + o_seg),
              *d_win = reinterpret_cast<uint32_t *>(b + o_win);
@@ -1022,22 +1049,16 @@ extern "C" int ga_arbitrate(ga_ctx *ctx, const uint32_t *seg_offsets, uint32_t n
     double *d_sc = reinterpret_cast<double *>(b + o_sc);
     rc = join_inflight(ctx, s);
     if (rc) return rc;
-    if (n_members) {
-        GA_CUDA_TRY(cudaMemcpyAsync(d_off, off.data(), 8ull * n_members, cudaMemcpyHostToDevice, s));
-        GA_CUDA_TRY(cudaMemcpyAsync(d_cnt, cnt.data(), 4ull * n_members, cudaMemcpyHostToDevice, s));
-        GA_CUDA_TRY(cudaMemcpyAsync(d_st, status_in, n_members, cudaMemcpyHostToDevice, s));
-        // scores of skipped relays stay what the caller passed in (audio_service.go:522-524)
-        GA_CUDA_TRY(cudaMemcpyAsync(d_sc, scores, 8ull * n_members, cudaMemcpyHostToDevice, s));
-    }
-    GA_CUDA_TRY(cudaMemcpyAsync(d_seg, seg_offsets, 4ull * (n_windows + 1), cudaMemcpyHostToDevice, s));
+    GA_CUDA_TRY(cudaMemcpyAsync(b, hb, o_win, cudaMemcpyHostToDevice, s));
     rc = ga_k_arbitrate(ctx->d_arena, d_off, d_cnt, d_st, d_seg, n_windows, n_members, d_sc, d_win, d_so, s);
     if (rc) return rc;
-    if (n_members) {
-        GA_CUDA_TRY(cudaMemcpyAsync(scores, d_sc, 8ull * n_members, cudaMemcpyDeviceToHost, s));
-        GA_CUDA_TRY(cudaMemcpyAsync(status_out, d_so, n_members, cudaMemcpyDeviceToHost, s));
-    }
-    GA_CUDA_TRY(cudaMemcpyAsync(winner_idx, d_win, 4ull * n_windows, cudaMemcpyDeviceToHost, s));
+    GA_CUDA_TRY(cudaMemcpyAsync(hb + o_sc, b + o_sc, end - o_sc, cudaMemcpyDeviceToHost, s));
     GA_CUDA_TRY(cudaStreamSynchronize(s));
+    if (n_members) {
+        std::memcpy(scores, hb + o_sc, 8ull * n_members);
+        std::memcpy(status_out, hb + o_so, n_members);
+    }
+    std::memcpy(winner_idx, hb + o_win, 4ull * n_windows);
     return GA_OK;
 }
 

@@ -41,6 +41,10 @@ for t in range(args.ticks):
     if t == wake - 1:                                         # the 300 ms windows close
         t0 = time.perf_counter()
         winner, scores, status = ctx.arbitrate(seg, sid)
+        arb_first = time.perf_counter() - t0                  # includes growing the context's tables
+        assert (winner == seg[:-1]).all()
+        t0 = time.perf_counter()
+        winner, scores, status = ctx.arbitrate(seg, sid)
         arb = time.perf_counter() - t0
         assert (winner == seg[:-1]).all()
 lat = np.array(lat[5:]) * 1e3
@@ -50,6 +54,6 @@ if args.utterance:
     assert ctx.utterance_digest(5) == (hashlib.sha256(whole).digest(), len(whole))
 print(json.dumps({"streams": S, "ticks": args.ticks, "utterance_digest": bool(args.utterance), "tick_latency_ms": {"median": float(np.median(lat)),
       "p99": float(np.percentile(lat, 99)), "max": float(lat.max())},
-      "arbitration_ms_all_windows": arb * 1e3, "windows": S // group,
+      "arbitration_ms_all_windows": arb * 1e3, "arbitration_ms_first_call": arb_first * 1e3, "windows": S // group,
       "real_time_budget_ms": 20.0, "h2d_bytes_per_tick": S * ms * 2 + S * 32, "d2h_bytes_per_tick": S * 64}))
 ctx.close()
