@@ -17,7 +17,10 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--streams", type=int, default=8192)
 ap.add_argument("--ticks", type=int, default=250)
 ap.add_argument("--utterance", action="store_true", help="also keep the per-utterance running SHA-256 (GA_DO_UTTERANCE)")
+ap.add_argument("--submit", default="ticks", choices=["ticks", "msgs"],
+                help="ga_submit_ticks (descriptors built on the GPU; mono contexts without the running digest) or ga_submit")
 args = ap.parse_args()
+use_ticks = args.submit == "ticks" and not args.utterance
 S, ms, wake, group = args.streams, 320, 15, 8
 pcm = api.synth_batch_host(synth.SEED, 0, S, group, args.ticks, ms, n_threads=8).reshape(args.ticks, S * ms)
 ctx = api.Context(device=0, max_streams=S, max_batch_msgs=S, max_inflight=2, ring_bytes=S * ms * 2 * 8,
@@ -35,8 +38,12 @@ for t in range(args.ticks):
     view[:S * ms * 2] = pcm[t].view(np.uint8)                 # the relays' chunks land in the ring (not timed)
     msgs["ring_offset"] = rel + np.uint64(off)
     msgs["flags"] = (L.MSG_WAKE if t < wake else 0) | (L.MSG_FIRST if t == 0 else 0)
+    tick_flags = np.full(S, int(msgs["flags"][0]), np.uint8)
     t0 = time.perf_counter()
-    res, _ = ctx.wait_view(ctx.submit(msgs))
+    if use_ticks:
+        res, _ = ctx.wait_view(ctx.submit_ticks(off, 1, sid, ms * 2, tick_flags))
+    else:
+        res, _ = ctx.wait_view(ctx.submit(msgs))
     lat.append(time.perf_counter() - t0)
     if t == wake - 1:                                         # the 300 ms windows close
         t0 = time.perf_counter()
@@ -52,8 +59,8 @@ if args.utterance:
     import hashlib
     whole = pcm.reshape(args.ticks, S, ms)[:, 5, :].tobytes()
     assert ctx.utterance_digest(5) == (hashlib.sha256(whole).digest(), len(whole))
-print(json.dumps({"streams": S, "ticks": args.ticks, "utterance_digest": bool(args.utterance), "tick_latency_ms": {"median": float(np.median(lat)),
+print(json.dumps({"streams": S, "ticks": args.ticks, "submit": "ga_submit_ticks" if use_ticks else "ga_submit", "utterance_digest": bool(args.utterance), "tick_latency_ms": {"median": float(np.median(lat)),
       "p99": float(np.percentile(lat, 99)), "max": float(lat.max())},
       "arbitration_ms_all_windows": arb * 1e3, "arbitration_ms_first_call": arb_first * 1e3, "windows": S // group,
-      "real_time_budget_ms": 20.0, "h2d_bytes_per_tick": S * ms * 2 + S * 32, "d2h_bytes_per_tick": S * 64}))
+      "real_time_budget_ms": 20.0, "h2d_bytes_per_tick": S * ms * 2 + (S * 13 if use_ticks else S * 32), "d2h_bytes_per_tick": S * 64}))
 ctx.close()
