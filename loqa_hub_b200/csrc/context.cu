@@ -265,12 +265,12 @@ extern "C" int ga_init(const ga_config *cfg, ga_ctx **out)
             GA_ALLOC_TRY(cudaHostAlloc(reinterpret_cast<void **>(&s.h_frames), sizeof(ga_frame) * c->frames_cap, cudaHostAllocDefault));
             GA_ALLOC_TRY(cudaMalloc(reinterpret_cast<void **>(&s.d_frames), sizeof(ga_frame) * c->frames_cap));
         }
-        if (!fmt48 && !utter) {
+        if (!fmt48) {
             GA_ALLOC_TRY(cudaHostAlloc(reinterpret_cast<void **>(&s.h_tick), tick_bytes(cfg->max_batch_msgs), cudaHostAllocDefault));
             GA_ALLOC_TRY(cudaMalloc(reinterpret_cast<void **>(&s.d_tick), tick_bytes(cfg->max_batch_msgs)));
         }
     }
-    if (!fmt48 && !utter) {
+    if (!fmt48) {
         try { c->tick_stamp.assign(cfg->max_streams, 0); }
         catch (...) { set_error("ga_init: out of host memory"); destroy(c); return GA_ERR_NOMEM; }
     }
@@ -596,10 +596,15 @@ __global__ void __launch_bounds__(256)
 tick_desc_kernel(const uint32_t *__restrict__ ids, const uint32_t *__restrict__ wake0,
                  const uint32_t *__restrict__ speech0, const uint8_t *__restrict__ flags, uint32_t n,
                  uint32_t n_streams, uint32_t chunk_bytes, uint32_t stride, uint64_t phys0, uint64_t arena,
-                 uint64_t wake_cap, uint32_t frames_per_msg, int convert, ga_desc *__restrict__ desc)
+                 uint64_t wake_cap, uint32_t frames_per_msg, int convert, ga_desc *__restrict__ desc,
+                 uint32_t *__restrict__ link_next, uint32_t *__restrict__ run_first)
 {
     const uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
     if (m >= n) return;
+    if (link_next) {                  // running digests: a stream's chunks of the batch, in order, start at period 0
+        link_next[m] = m + n_streams < n ? m + n_streams : 0xffffffffu;
+        if (m < n_streams) run_first[m] = m;
+    }
     const uint32_t t = m / n_streams, j = m - t * n_streams, ns = chunk_bytes >> 1;
     uint32_t w = wake0[j], s = speech0[j];
     if (flags) {
@@ -643,11 +648,12 @@ extern "C" int ga_submit_ticks(ga_ctx *ctx, uint64_t ring_offset, uint32_t n_tic
     const uint32_t n = static_cast<uint32_t>(n64);
     std::lock_guard<std::mutex> lk(ctx->mu);
     if (ctx->tick_stamp.empty()) {
-        set_error("ga_submit_ticks: only for mono 16 kHz contexts without GA_DO_UTTERANCE; use ga_submit");
+        set_error("ga_submit_ticks: only for mono 16 kHz contexts; use ga_submit");
         return GA_ERR_STATE;
     }
     const uint64_t arena = ctx->cfg.arena_samples, wake_cap = ctx->cfg.wake_samples_max;
     const bool convert = (ctx->cfg.mode & GA_DO_CONVERT) != 0;
+    const bool utter = (ctx->cfg.mode & GA_DO_UTTERANCE) != 0;
     if (convert && arena > 0xffffffffull) { set_error("ga_submit_ticks: arena_samples beyond 2^32; use ga_submit"); return GA_ERR_STATE; }
     int rc = set_device(ctx);
     if (rc) return rc;
@@ -731,15 +737,27 @@ extern "C" int ga_submit_ticks(ga_ctx *ctx, uint64_t ring_offset, uint32_t n_tic
         GA_CUDA_TRY(cudaMemcpyAsync(slot->d_tick, slot->h_tick, 12ull * n_streams + (flags ? n : 0), cudaMemcpyHostToDevice, s));
         tick_desc_kernel<<<(n + 255) / 256, 256, 0, s>>>(d_ids, d_wake0, d_speech0, flags ? d_flags : nullptr, n, n_streams, chunk_bytes,
                                                         static_cast<uint32_t>(stride), phys0, arena, wake_cap,
-                                                        static_cast<uint32_t>(frames_per_msg), convert ? 1 : 0, slot->d_desc);
+                                                        static_cast<uint32_t>(frames_per_msg), convert ? 1 : 0, slot->d_desc,
+                                                        utter ? slot->d_link : nullptr,
+                                                        utter ? slot->d_link + ctx->cfg.max_batch_msgs : nullptr);
         GA_CHECK_LAUNCH("tick_desc_kernel");
-        if (chunk_bytes && ctx->cfg.staging != GA_STAGING_BULK)
+        if (!(ctx->cfg.mode & GA_DO_ALL))
+            GA_CUDA_TRY(cudaMemsetAsync(slot->d_res, 0, sizeof(ga_result) * n, s));
+        else if (chunk_bytes && ctx->cfg.staging != GA_STAGING_BULK)
             r = ga_k_ingest_uniform(ctx->d_ring, slot->d_desc, n, phys0, chunk_bytes, stride, ctx->d_arena, slot->d_res,
                                     ctx->frames_cap ? slot->d_frames : nullptr, ctx->cfg.mode & GA_DO_ALL, ctx->cfg.vad_threshold, s);
         else
             r = ga_k_ingest(ctx->d_ring, slot->d_desc, n, ctx->d_arena, slot->d_res,
                             ctx->frames_cap ? slot->d_frames : nullptr, ctx->cfg.mode & GA_DO_ALL, ctx->cfg.vad_threshold, s);
         if (r) return r;
+        if (utter) {
+            // the running digests make consecutive tickets dependent, as in ga_submit
+            if (ctx->prev_kdone) GA_CUDA_TRY(cudaStreamWaitEvent(s, ctx->prev_kdone, 0));
+            r = ga_k_sha256_chain(ctx->d_ring, slot->d_desc, slot->d_link + ctx->cfg.max_batch_msgs, slot->d_link, n_streams, ctx->d_sha, s);
+            if (r) return r;
+            GA_CUDA_TRY(cudaEventRecord(slot->kdone, s));
+            ctx->prev_kdone = slot->kdone;
+        }
         GA_CUDA_TRY(cudaMemcpyAsync(slot->h_res, slot->d_res, sizeof(ga_result) * n, cudaMemcpyDeviceToHost, s));
         if (ctx->frames_cap && frames)
             GA_CUDA_TRY(cudaMemcpyAsync(slot->h_frames, slot->d_frames, sizeof(ga_frame) * frames, cudaMemcpyDeviceToHost, s));

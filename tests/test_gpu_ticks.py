@@ -116,12 +116,38 @@ def test_refused_calls_leave_the_context_as_it_was():
         assert np.array_equal(c.fetch_samples(0, 400, 200), ora.bytes_to_float32(pcm[0].tobytes())[0])
 
 
-def test_not_offered_where_the_host_must_thread_state():
-    with make(mode=L.DO_ALL | L.DO_UTTERANCE) as c:
-        _, off = c.reserve(6400)
-        with pytest.raises(L.GpuAudioError) as e:
-            c.submit_ticks(off, 1, np.arange(10, dtype=np.uint32), 640)
-        assert e.value.code == L.GA_ERR_STATE
+@pytest.mark.parametrize("mode", [L.DO_ALL | L.DO_UTTERANCE, L.DO_UTTERANCE])
+def test_running_utterance_digests_through_tick_batches(mode):
+    """GA_DO_UTTERANCE contexts: the per-stream lists the digest kernel walks are laid out on the GPU
+    too; digests after several tick batches (a restart in between) equal hashlib over the bytes."""
+    import hashlib
+    rng = np.random.default_rng(77)
+    ids = np.array([9, 2, 40, 17, 5], dtype=np.uint32)
+    S, chunk = ids.size, 650                                    # 650 B: the carried tail is exercised
+    got = {int(s): b"" for s in ids}
+    with make(mode=mode, want_frames=False) as c:
+        for rnd, n_ticks in enumerate((3, 1, 4, 2)):
+            n = n_ticks * S
+            pcm = rng.integers(0, 256, size=(n, chunk), dtype=np.uint8)
+            flags = np.zeros((n_ticks, S), np.uint8)
+            if rnd == 0:
+                flags[0] = L.MSG_FIRST
+            if rnd == 2:
+                flags[0, 1] = L.MSG_FIRST                        # stream 2 starts a new utterance
+                got[2] = b""
+            off, _ = lay_out(c, pcm, n, chunk)
+            res, _ = c.wait(c.submit_ticks(off, n_ticks, ids, chunk, flags.reshape(-1)))
+            for t in range(n_ticks):
+                for j, sid in enumerate(ids):
+                    got[int(sid)] += pcm[t * S + j].tobytes()
+            if mode & L.DO_SHA256:
+                assert res["digest"][n - 1].tobytes() == hashlib.sha256(pcm[n - 1].tobytes()).digest()
+            for sid in ids:
+                d, nbytes = c.utterance_digest(int(sid))
+                assert (bytes(d), nbytes) == (hashlib.sha256(got[int(sid)]).digest(), len(got[int(sid)])), (rnd, sid)
+
+
+def test_not_offered_for_48k_input():
     with make(input_format=L.FMT_STEREO48K, arena_samples=40_000) as c:
         _, off = c.reserve(6400)
         with pytest.raises(L.GpuAudioError) as e:
