@@ -519,11 +519,11 @@ def run_e2e(args, w, plan, pcm, arbitration, d_winner, world, rank, local_rank, 
 
     def wait(t):       # zero-copy: the result records stay in the C-owned pinned buffer
         L.check(lib.ga_wait_view(ctx._h, t, C.byref(res_p), None, C.byref(res_n), None))
-    ticks = args.submit == "ticks" and not fmt48       # ga_submit_ticks is for mono contexts
+    ticks = args.submit == "ticks"
     ids = np.arange(S, dtype=np.uint32)
     tick_flags = [np.ascontiguousarray(mm["flags"].astype(np.uint8)) for mm in msgs]
-    # per-message descriptors (32 B each) or, for ga_submit_ticks, 1 flag byte per message + 12 B per stream
-    h2d = sub_bytes * n_sub + (n_sub * (sub_msgs + 12 * S) if ticks else sub_msgs * n_sub * (96 if fmt48 else 32))
+    # per-message descriptors (32 B each, 96 B for 48 kHz) or, for ga_submit_ticks, 1 flag byte per message + 20 B per stream
+    h2d = sub_bytes * n_sub + (n_sub * (sub_msgs + 20 * S) if ticks else sub_msgs * n_sub * (96 if fmt48 else 32))
     d2h = sub_msgs * n_sub * 64 + plan.n_windows * 4
 
     def one_step(fill):
@@ -534,7 +534,7 @@ def run_e2e(args, w, plan, pcm, arbitration, d_winner, world, rank, local_rank, 
                 view[:sub_bytes] = host_pcm[(j % n_host) * sub_bytes:(j % n_host + 1) * sub_bytes]
             t = C.c_uint64()
             if ticks:
-                L.check(lib.ga_submit_ticks(ctx._h, off, tps, S, ms * 2, L.ptr(ids), L.ptr(tick_flags[j]), C.byref(t)))
+                L.check(lib.ga_submit_ticks(ctx._h, off, tps, S, chunk, L.ptr(ids), L.ptr(tick_flags[j]), C.byref(t)))
             else:
                 mm = msgs[j]
                 mm["ring_offset"] = rel + np.uint64(off)

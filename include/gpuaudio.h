@@ -357,7 +357,9 @@ int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *ticket);
  * distinct.  The per-message descriptors are built on the GPU from the per-stream cursors, so
  * the host sends 1 byte per message and 12 per stream instead of 32 per message.  Results come
  * back exactly as from ga_submit of the same n_ticks * n_streams messages, the running utterance
- * digests (GA_DO_UTTERANCE) included.  Mono 16 kHz contexts only (GA_ERR_STATE otherwise). */
+ * digests (GA_DO_UTTERANCE) included.  48 kHz stereo contexts take chunks that are a multiple of
+ * 12 bytes in [192, GA_RS_MAX_MSG_BYTES] (whole groups of three frames, at least the filter
+ * history); other sizes go through ga_submit. */
 int ga_submit_ticks(ga_ctx *ctx, uint64_t ring_offset, uint32_t n_ticks, uint32_t n_streams,
                     uint32_t chunk_bytes, const uint32_t *stream_ids, const uint8_t *flags,
                     uint64_t *ticket);

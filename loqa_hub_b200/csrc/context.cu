@@ -138,8 +138,9 @@ static void destroy(ga_ctx *c)
     delete c;
 }
 
-// ga_submit_ticks side buffer: three u32 arrays of up to cap streams, then cap flag bytes
-static size_t tick_bytes(uint32_t cap) { return (static_cast<size_t>(cap) * 13u + 63u) & ~static_cast<size_t>(63); }
+// ga_submit_ticks side buffer: five u32 arrays of up to cap streams (ids, wake0, speech0 and, for
+// 48 kHz input, the two halves of the stream's frame count), then cap flag bytes
+static size_t tick_bytes(uint32_t cap) { return (static_cast<size_t>(cap) * 21u + 63u) & ~static_cast<size_t>(63); }
 
 #define GA_ALLOC_TRY(expr)                                                            \
     do {                                                                              \
@@ -265,12 +266,12 @@ extern "C" int ga_init(const ga_config *cfg, ga_ctx **out)
             GA_ALLOC_TRY(cudaHostAlloc(reinterpret_cast<void **>(&s.h_frames), sizeof(ga_frame) * c->frames_cap, cudaHostAllocDefault));
             GA_ALLOC_TRY(cudaMalloc(reinterpret_cast<void **>(&s.d_frames), sizeof(ga_frame) * c->frames_cap));
         }
-        if (!fmt48) {
+        {
             GA_ALLOC_TRY(cudaHostAlloc(reinterpret_cast<void **>(&s.h_tick), tick_bytes(cfg->max_batch_msgs), cudaHostAllocDefault));
             GA_ALLOC_TRY(cudaMalloc(reinterpret_cast<void **>(&s.d_tick), tick_bytes(cfg->max_batch_msgs)));
         }
     }
-    if (!fmt48) {
+    {
         try { c->tick_stamp.assign(cfg->max_streams, 0); }
         catch (...) { set_error("ga_init: out of host memory"); destroy(c); return GA_ERR_NOMEM; }
     }
@@ -597,7 +598,9 @@ tick_desc_kernel(const uint32_t *__restrict__ ids, const uint32_t *__restrict__ 
                  const uint32_t *__restrict__ speech0, const uint8_t *__restrict__ flags, uint32_t n,
                  uint32_t n_streams, uint32_t chunk_bytes, uint32_t stride, uint64_t phys0, uint64_t arena,
                  uint64_t wake_cap, uint32_t frames_per_msg, int convert, ga_desc *__restrict__ desc,
-                 uint32_t *__restrict__ link_next, uint32_t *__restrict__ run_first)
+                 uint32_t *__restrict__ link_next, uint32_t *__restrict__ run_first,
+                 ga_rdesc *__restrict__ rdesc, const uint32_t *__restrict__ n0_lo, const uint32_t *__restrict__ n0_hi,
+                 uint32_t n_ticks)
 {
     const uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
     if (m >= n) return;
@@ -605,7 +608,9 @@ tick_desc_kernel(const uint32_t *__restrict__ ids, const uint32_t *__restrict__ 
         link_next[m] = m + n_streams < n ? m + n_streams : 0xffffffffu;
         if (m < n_streams) run_first[m] = m;
     }
-    const uint32_t t = m / n_streams, j = m - t * n_streams, ns = chunk_bytes >> 1;
+    const uint32_t t = m / n_streams, j = m - t * n_streams;
+    // 48 kHz stereo chunks of 3k frames give k outputs each, wherever the stream stands
+    const uint32_t ns = rdesc ? chunk_bytes / 12u : chunk_bytes >> 1;
     uint32_t w = wake0[j], s = speech0[j];
     if (flags) {
         for (uint32_t k = 0; k < t; k++) {
@@ -630,6 +635,32 @@ tick_desc_kernel(const uint32_t *__restrict__ ids, const uint32_t *__restrict__ 
     const uint4 *v = reinterpret_cast<const uint4 *>(&d);
     o[0] = v[0];
     o[1] = v[1];
+    if (rdesc) {
+        // decimator descriptor: position on the stream's frame timeline and where the 47 frames
+        // before the chunk come from.  A restart is only possible in period 0 here (conversion is on).
+        const uint32_t frames = chunk_bytes >> 2;
+        const bool first = flags && (flags[j] & GA_MSG_FIRST);
+        const uint64_t base = first ? 0ull : (static_cast<uint64_t>(n0_hi[j]) << 32) | n0_lo[j];
+        ga_rdesc r;
+        r.in_off = d.in_off;
+        r.out_off = d.out_off;
+        r.n0 = base + static_cast<uint64_t>(t) * frames;
+        r.nbytes = chunk_bytes;
+        r.stream_id = id;
+        r.flags = f | (t + 1 == n_ticks ? GA_RS_SAVE_HIST : 0u);    // only the stream's last chunk of the batch saves
+        r.frame_off = d.frame_off;
+        r.reserved[0] = r.reserved[1] = r.reserved[2] = 0;
+        if (t > 0) {
+            r.hist_kind = GA_HIST_SLAB;                                // tail of the stream's previous chunk, one period back
+            r.hist_off = d.in_off - static_cast<uint64_t>(n_streams) * stride + static_cast<uint64_t>(frames - 47u) * 4u;
+        } else {
+            r.hist_kind = (first || base == 0) ? GA_HIST_ZERO : GA_HIST_STATE;
+            r.hist_off = 0;
+        }
+        uint4 *ro = reinterpret_cast<uint4 *>(rdesc + m);
+        const uint4 *rv = reinterpret_cast<const uint4 *>(&r);
+        ro[0] = rv[0]; ro[1] = rv[1]; ro[2] = rv[2]; ro[3] = rv[3];
+    }
 }
 
 }  // namespace ga
@@ -647,9 +678,12 @@ extern "C" int ga_submit_ticks(ga_ctx *ctx, uint64_t ring_offset, uint32_t n_tic
     }
     const uint32_t n = static_cast<uint32_t>(n64);
     std::lock_guard<std::mutex> lk(ctx->mu);
-    if (ctx->tick_stamp.empty()) {
-        set_error("ga_submit_ticks: only for mono 16 kHz contexts; use ga_submit");
-        return GA_ERR_STATE;
+    const bool fmt48 = ctx->cfg.input_format == GA_FMT_STEREO48K;
+    if (fmt48 && (chunk_bytes % 12u != 0 || chunk_bytes < 47u * 4u || chunk_bytes > GA_RS_MAX_MSG_BYTES)) {
+        // whole groups of 3 stereo frames (so every chunk yields the same number of outputs) and at
+        // least the 47 frames of filter history the next period takes from the slab
+        set_error("ga_submit_ticks: 48 kHz chunks must be a multiple of 12 bytes in [192, %u]; use ga_submit", GA_RS_MAX_MSG_BYTES);
+        return GA_ERR_ARG;
     }
     const uint64_t arena = ctx->cfg.arena_samples, wake_cap = ctx->cfg.wake_samples_max;
     const bool convert = (ctx->cfg.mode & GA_DO_CONVERT) != 0;
@@ -670,10 +704,11 @@ extern "C" int ga_submit_ticks(ga_ctx *ctx, uint64_t ring_offset, uint32_t n_tic
         set_error("ga_submit_ticks: [%llu, +%llu) is not one live reservation", (unsigned long long)ring_offset, (unsigned long long)span);
         return GA_ERR_ARG;
     }
-    // side buffer, packed so that one copy moves it: ids | wake0 | speech0 (n_streams each) | flags (n)
+    // side buffer, packed so that one copy moves it: ids | wake0 | speech0 | n0 lo | n0 hi (n_streams each) | flags (n)
     uint32_t *h_ids = reinterpret_cast<uint32_t *>(slot->h_tick), *h_wake0 = h_ids + n_streams, *h_speech0 = h_wake0 + n_streams;
-    uint8_t *h_flags = reinterpret_cast<uint8_t *>(h_speech0 + n_streams);
-    const uint64_t ns = chunk_bytes >> 1, frames_per_msg = (ns + GA_FRAME_SAMPLES - 1) / GA_FRAME_SAMPLES;
+    uint32_t *h_n0lo = h_speech0 + n_streams, *h_n0hi = h_n0lo + n_streams;
+    uint8_t *h_flags = reinterpret_cast<uint8_t *>(h_n0hi + n_streams);
+    const uint64_t ns = fmt48 ? chunk_bytes / 12u : chunk_bytes >> 1, frames_per_msg = (ns + GA_FRAME_SAMPLES - 1) / GA_FRAME_SAMPLES;
     const uint64_t frames = frames_per_msg * n;
     if (ctx->frames_cap && frames > ctx->frames_cap) {
         set_error("ga_submit_ticks: batch needs %llu frame records, capacity %llu", (unsigned long long)frames, (unsigned long long)ctx->frames_cap);
@@ -697,6 +732,8 @@ extern "C" int ga_submit_ticks(ga_ctx *ctx, uint64_t ring_offset, uint32_t n_tic
         h_ids[j] = id;
         h_wake0[j] = static_cast<uint32_t>(st.wake_n);
         h_speech0[j] = static_cast<uint32_t>(st.speech_n);
+        h_n0lo[j] = static_cast<uint32_t>(st.n_frames);
+        h_n0hi[j] = static_cast<uint32_t>(st.n_frames >> 32);
         for (uint32_t t = 0; t < n_ticks; t++) {
             const uint32_t f = flags ? flags[static_cast<size_t>(t) * n_streams + j] : 0u;
             if (f & GA_MSG_FIRST) {
@@ -717,6 +754,7 @@ extern "C" int ga_submit_ticks(ga_ctx *ctx, uint64_t ring_offset, uint32_t n_tic
                 break;
             }
             cursor += ns;
+            if (fmt48) st.n_frames += chunk_bytes >> 2;
         }
         if (err) { st = before[j]; ctx->tick_stamp[id] = 0; }
         else st.stamp = stamp;
@@ -733,15 +771,33 @@ extern "C" int ga_submit_ticks(ga_ctx *ctx, uint64_t ring_offset, uint32_t n_tic
         if (r) return r;
         if (span) GA_CUDA_TRY(cudaMemcpyAsync(ctx->d_ring + phys0, ctx->h_ring + phys0, span, cudaMemcpyHostToDevice, s));
         uint32_t *d_ids = reinterpret_cast<uint32_t *>(slot->d_tick), *d_wake0 = d_ids + n_streams, *d_speech0 = d_wake0 + n_streams;
-        uint8_t *d_flags = reinterpret_cast<uint8_t *>(d_speech0 + n_streams);
-        GA_CUDA_TRY(cudaMemcpyAsync(slot->d_tick, slot->h_tick, 12ull * n_streams + (flags ? n : 0), cudaMemcpyHostToDevice, s));
+        uint32_t *d_n0lo = d_speech0 + n_streams, *d_n0hi = d_n0lo + n_streams;
+        uint8_t *d_flags = reinterpret_cast<uint8_t *>(d_n0hi + n_streams);
+        GA_CUDA_TRY(cudaMemcpyAsync(slot->d_tick, slot->h_tick, 20ull * n_streams + (flags ? n : 0), cudaMemcpyHostToDevice, s));
         tick_desc_kernel<<<(n + 255) / 256, 256, 0, s>>>(d_ids, d_wake0, d_speech0, flags ? d_flags : nullptr, n, n_streams, chunk_bytes,
                                                         static_cast<uint32_t>(stride), phys0, arena, wake_cap,
                                                         static_cast<uint32_t>(frames_per_msg), convert ? 1 : 0, slot->d_desc,
                                                         utter ? slot->d_link : nullptr,
-                                                        utter ? slot->d_link + ctx->cfg.max_batch_msgs : nullptr);
+                                                        utter ? slot->d_link + ctx->cfg.max_batch_msgs : nullptr,
+                                                        fmt48 ? slot->d_rdesc : nullptr, d_n0lo, d_n0hi, n_ticks);
         GA_CHECK_LAUNCH("tick_desc_kernel");
-        if (!(ctx->cfg.mode & GA_DO_ALL))
+        if (fmt48) {
+            // as in ga_submit: fingerprint of the received bytes (whole records), then the decimator
+            // fills in the statistics; its per-stream history chains consecutive tickets
+            if (ctx->cfg.mode & GA_DO_SHA256) {
+                if (ctx->cfg.staging != GA_STAGING_BULK)
+                    r = ga_k_ingest_uniform(ctx->d_ring, slot->d_desc, n, phys0, chunk_bytes, stride, nullptr, slot->d_res, nullptr,
+                                            GA_DO_SHA256, ctx->cfg.vad_threshold, s);
+                else
+                    r = ga_k_ingest(ctx->d_ring, slot->d_desc, n, nullptr, slot->d_res, nullptr, GA_DO_SHA256, ctx->cfg.vad_threshold, s);
+                if (r) return r;
+            } else {
+                GA_CUDA_TRY(cudaMemsetAsync(slot->d_res, 0, sizeof(ga_result) * n, s));
+            }
+            if (ctx->prev_kdone) GA_CUDA_TRY(cudaStreamWaitEvent(s, ctx->prev_kdone, 0));
+            r = ga_k_resample48(ctx->d_ring, slot->d_rdesc, n, ctx->d_hist, ctx->d_arena, slot->d_res,
+                                ctx->frames_cap ? slot->d_frames : nullptr, ctx->cfg.vad_threshold, s);
+        } else if (!(ctx->cfg.mode & GA_DO_ALL))
             GA_CUDA_TRY(cudaMemsetAsync(slot->d_res, 0, sizeof(ga_result) * n, s));
         else if (chunk_bytes && ctx->cfg.staging != GA_STAGING_BULK)
             r = ga_k_ingest_uniform(ctx->d_ring, slot->d_desc, n, phys0, chunk_bytes, stride, ctx->d_arena, slot->d_res,
@@ -752,9 +808,11 @@ extern "C" int ga_submit_ticks(ga_ctx *ctx, uint64_t ring_offset, uint32_t n_tic
         if (r) return r;
         if (utter) {
             // the running digests make consecutive tickets dependent, as in ga_submit
-            if (ctx->prev_kdone) GA_CUDA_TRY(cudaStreamWaitEvent(s, ctx->prev_kdone, 0));
+            if (ctx->prev_kdone && !fmt48) GA_CUDA_TRY(cudaStreamWaitEvent(s, ctx->prev_kdone, 0));
             r = ga_k_sha256_chain(ctx->d_ring, slot->d_desc, slot->d_link + ctx->cfg.max_batch_msgs, slot->d_link, n_streams, ctx->d_sha, s);
             if (r) return r;
+        }
+        if (fmt48 || utter) {
             GA_CUDA_TRY(cudaEventRecord(slot->kdone, s));
             ctx->prev_kdone = slot->kdone;
         }

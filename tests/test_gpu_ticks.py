@@ -147,12 +147,50 @@ def test_running_utterance_digests_through_tick_batches(mode):
                 assert (bytes(d), nbytes) == (hashlib.sha256(got[int(sid)]).digest(), len(got[int(sid)])), (rnd, sid)
 
 
-def test_not_offered_for_48k_input():
+@pytest.mark.parametrize("chunk,utter", [(3840, False), (1920, True), (192, False)])
+def test_48k_tick_batches_match_per_message_submit(chunk, utter):
+    """48 kHz stereo contexts: the decimator's descriptors (position on the stream's frame timeline,
+    where the 47 frames of history come from, who saves it) are built on the GPU as well.  Two tick
+    batches, then a ragged chunk through ga_submit on both contexts: the carried state must agree."""
+    rng = np.random.default_rng(chunk)
+    ids = np.array([7, 1, 30, 12], dtype=np.uint32)
+    S = ids.size
+    mode = L.DO_ALL | (L.DO_UTTERANCE if utter else 0)
+    kw = dict(mode=mode, input_format=L.FMT_STEREO48K, arena_samples=40_000, wake_samples_max=8_000)
+    with make(**kw) as a, make(**kw) as b:
+        for rnd, n_ticks in enumerate((3, 2)):
+            n = n_ticks * S
+            pcm = rng.integers(0, 256, size=(n, chunk), dtype=np.uint8)
+            flags = np.zeros((n_ticks, S), np.uint8)
+            flags[:1] |= L.MSG_WAKE
+            if rnd == 0:
+                flags[0] |= L.MSG_FIRST
+            off_a, stride = lay_out(a, pcm, n, chunk)
+            off_b, _ = lay_out(b, pcm, n, chunk)
+            ra, fa = a.wait(a.submit_ticks(off_a, n_ticks, ids, chunk, flags.reshape(-1)))
+            rb, fb = b.wait(b.submit(per_message(off_b, stride, chunk, ids, flags.reshape(-1), n_ticks)))
+            same_records(ra, rb)
+            assert fa.tobytes() == fb.tobytes()
+        tail = rng.integers(0, 256, size=4 * 101 + 3, dtype=np.uint8).tobytes()      # ragged, history from the saved state
+        ra, _ = a.ingest([tail] * S, ids, [0] * S)
+        rb, _ = b.ingest([tail] * S, ids, [0] * S)
+        same_records(ra, rb)
+        for sid in ids:
+            assert a.stream_info(int(sid)) == b.stream_info(int(sid))
+            assert a.fetch_samples(int(sid)).tobytes() == b.fetch_samples(int(sid)).tobytes()
+            if utter:
+                assert a.utterance_digest(int(sid)) == b.utterance_digest(int(sid))
+        assert a.stream_info(7)[0] == 5 * (chunk // 12) + 33        # 5 tick chunks + the 101-frame tail
+
+
+def test_48k_tick_batches_need_whole_groups_of_three_frames():
     with make(input_format=L.FMT_STEREO48K, arena_samples=40_000) as c:
-        _, off = c.reserve(6400)
-        with pytest.raises(L.GpuAudioError) as e:
-            c.submit_ticks(off, 1, np.arange(10, dtype=np.uint32), 640)
-        assert e.value.code == L.GA_ERR_STATE
+        _, off = c.reserve(64_000)
+        for bad in (640, 3838, 188, 3852, 0):
+            with pytest.raises(L.GpuAudioError) as e:
+                c.submit_ticks(off, 1, np.arange(10, dtype=np.uint32), bad)
+            assert e.value.code == L.GA_ERR_ARG and "multiple of 12" in str(e.value)
+        assert [c.stream_info(i) for i in range(10)] == [(0, 0)] * 10
 
 
 def test_restarting_an_utterance_inside_a_batch():

@@ -18,9 +18,9 @@ ap.add_argument("--streams", type=int, default=8192)
 ap.add_argument("--ticks", type=int, default=250)
 ap.add_argument("--utterance", action="store_true", help="also keep the per-utterance running SHA-256 (GA_DO_UTTERANCE)")
 ap.add_argument("--submit", default="ticks", choices=["ticks", "msgs"],
-                help="ga_submit_ticks (descriptors built on the GPU; mono contexts without the running digest) or ga_submit")
+                help="ga_submit_ticks (descriptors built on the GPU) or ga_submit")
 args = ap.parse_args()
-use_ticks = args.submit == "ticks" and not args.utterance
+use_ticks = args.submit == "ticks"
 S, ms, wake, group = args.streams, 320, 15, 8
 pcm = api.synth_batch_host(synth.SEED, 0, S, group, args.ticks, ms, n_threads=8).reshape(args.ticks, S * ms)
 ctx = api.Context(device=0, max_streams=S, max_batch_msgs=S, max_inflight=2, ring_bytes=S * ms * 2 * 8,
