@@ -221,3 +221,63 @@ def test_any_set_of_windows_arbitrates_like_the_reference(windows, seed, twin):
             else:
                 assert scores[m] == -1.0           # relay.SignalStrength untouched for skipped relays
         assert list(st_out[lo:hi]) == list(so)
+
+
+# ---------------------------------------------------------------- tick batches vs per-message batches
+_pairs = {}
+
+
+@settings(max_examples=80, deadline=None, derandomize=True,
+          suppress_health_check=[HealthCheck.too_slow, HealthCheck.data_too_large])
+@given(fmt48=st.booleans(), utter=st.booleans(), n_streams=st.integers(1, 12),
+       ticks=st.lists(st.integers(1, 5), min_size=1, max_size=3), wake_ticks=st.integers(0, 3),
+       chunk16=st.sampled_from([0, 2, 64, 640, 642, 1000, 1281]), chunk48=st.sampled_from([192, 960, 1920, 3840]),
+       seed=st.integers(0, 2 ** 31))
+def test_tick_batches_equal_per_message_batches(fmt48, utter, n_streams, ticks, wake_ticks, chunk16, chunk48, seed):
+    """ga_submit_ticks (descriptors, decimator descriptors and digest lists built on the GPU) and
+    ga_submit (built on the host) on the same chunks, over consecutive batches of one utterance:
+    records, arenas, cursors and running digests must be identical."""
+    key = (fmt48, utter)
+    if key not in _pairs:
+        import __graft_entry__ as entry
+        entry.build()
+        kw = dict(device=0, max_streams=N_STREAMS, max_batch_msgs=64, max_inflight=2, ring_bytes=1 << 20,
+                  arena_samples=40_000, wake_samples_max=16_000, mode=L.DO_ALL | (L.DO_UTTERANCE if utter else 0),
+                  want_frames=True, input_format=L.FMT_STEREO48K if fmt48 else L.FMT_MONO16K)
+        _pairs[key] = (api.Context(**kw), api.Context(**kw))
+        _ctx[("pair-a",) + key], _ctx[("pair-b",) + key] = _pairs[key]      # closed with the module
+    a, b = _pairs[key]
+    rng = np.random.default_rng(seed)
+    chunk = chunk48 if fmt48 else chunk16
+    stride = (chunk + 15) & ~15
+    ids = rng.permutation(N_STREAMS)[:n_streams].astype(np.uint32)
+    done = 0
+    for rnd, T in enumerate(ticks):
+        n = T * n_streams
+        pcm = rng.integers(0, 256, size=(n, chunk), dtype=np.uint8)
+        flags = np.zeros((T, n_streams), np.uint8)
+        for t in range(T):
+            if done + t < wake_ticks:
+                flags[t] |= L.MSG_WAKE
+        if rnd == 0:
+            flags[0] |= L.MSG_FIRST
+        done += T
+        offs = []
+        for c in (a, b):
+            view, off = c.reserve(max(stride * n, 1))
+            for m in range(n):
+                view[m * stride:m * stride + chunk] = pcm[m]
+            offs.append(off)
+        ra, fa = a.wait(a.submit_ticks(offs[0], T, ids, chunk, flags.reshape(-1)))
+        msgs = np.zeros(n, dtype=L.MSG_DTYPE)
+        msgs["ring_offset"] = offs[1] + np.arange(n, dtype=np.uint64) * np.uint64(stride)
+        msgs["nbytes"] = chunk
+        msgs["stream_id"] = np.tile(ids, T)
+        msgs["flags"] = flags.reshape(-1)
+        rb, fb = b.wait(b.submit(msgs))
+        assert ra.tobytes() == rb.tobytes() and fa.tobytes() == fb.tobytes()
+    for sid in ids:
+        assert a.stream_info(int(sid)) == b.stream_info(int(sid))
+        assert a.fetch_samples(int(sid)).tobytes() == b.fetch_samples(int(sid)).tobytes()
+        if utter:
+            assert a.utterance_digest(int(sid)) == b.utterance_digest(int(sid))
