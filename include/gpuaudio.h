@@ -447,7 +447,7 @@ int  ga_hub_window_info(ga_hub *hub, uint64_t window_id, int *is_active, char *w
 int  ga_hub_active_window(ga_hub *hub, uint32_t group, uint64_t *window_id);   /* 0 = nil */
 int  ga_hub_relay_info(ga_hub *hub, const char *relay_id, int *status, double *signal_strength,
                        int *cancel_closed, uint32_t *slot);
-int  ga_hub_is_relay_active(ga_hub *hub, const char *relay_id);                /* isRelayActive :880-913 */
+int  ga_hub_is_relay_active(ga_hub *hub, const char *relay_id);                /* isRelayActive :880-913: 1 / 0, negative = error */
 int  ga_hub_set_relay_status(ga_hub *hub, const char *relay_id, int status);   /* as.activeStreams[id].Status = … */
 int  ga_hub_complete_request(ga_hub *hub, const char *relay_id);               /* collision_detection_test.go:361-369 */
 int  ga_hub_cleanup_relay(ga_hub *hub, const char *relay_id);                  /* cleanupRelay :916-923 */

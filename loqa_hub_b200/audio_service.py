@@ -112,7 +112,10 @@ class AudioService:
         return RelayInfo(st.value, sig.value, bool(cc.value), slot.value)
 
     def is_relay_active(self, relay_id):
-        return bool(L.load().ga_hub_is_relay_active(self._h, relay_id.encode()))
+        r = L.load().ga_hub_is_relay_active(self._h, relay_id.encode())
+        if r < 0:
+            L.check(r)
+        return bool(r)
 
     def set_relay_status(self, relay_id, status):
         L.check(L.load().ga_hub_set_relay_status(self._h, relay_id.encode(), status))

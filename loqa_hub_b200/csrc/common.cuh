@@ -3,6 +3,7 @@
 
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <new>
 
 #include <atomic>
 #include <cstdarg>
@@ -25,6 +26,18 @@ extern std::atomic<uint64_t> g_launches;
             return GA_ERR_CUDA;                                                       \
         }                                                                             \
     } while (0)
+
+// The C ABI never lets a C++ exception out (it would terminate the hub): every entry point that
+// can allocate on the host wraps its body in these.
+#define GA_GUARD_BEGIN try {
+#define GA_GUARD_END                                                                   \
+    } catch (const std::bad_alloc &) {                                                 \
+        ga::set_error("%s: out of host memory", __func__);                             \
+        return GA_ERR_NOMEM;                                                           \
+    } catch (...) {                                                                    \
+        ga::set_error("%s: unexpected C++ exception", __func__);                       \
+        return GA_ERR_STATE;                                                           \
+    }
 
 #define GA_CHECK_LAUNCH(name)                                                         \
     do {                                                                              \

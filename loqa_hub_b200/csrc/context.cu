@@ -185,6 +185,7 @@ static int arb_reserve(ga_ctx *ctx, size_t need);
 
 extern "C" int ga_init(const ga_config *cfg, ga_ctx **out)
 {
+    GA_GUARD_BEGIN
     if (!cfg || !out) { set_error("ga_init: NULL argument"); return GA_ERR_ARG; }
     *out = nullptr;
     if (cfg->max_streams == 0 || cfg->max_batch_msgs == 0 || cfg->ring_bytes < 4096 ||
@@ -279,6 +280,7 @@ extern "C" int ga_init(const ga_config *cfg, ga_ctx **out)
     if ((cfg->mode & GA_DO_CONVERT) && arb_reserve(c, 26ull * cfg->max_streams + 4096) != GA_OK) { destroy(c); return GA_ERR_NOMEM; }
     *out = c;
     return GA_OK;
+    GA_GUARD_END
 }
 
 extern "C" void ga_shutdown(ga_ctx *ctx) { destroy(ctx); }
@@ -323,6 +325,7 @@ static int fence_wait(ga_ctx *ctx, cudaStream_t s, uint64_t fence)
 
 extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *ticket)
 {
+    GA_GUARD_BEGIN
     if (!ctx || !ticket || (n && !msgs)) { set_error("ga_submit: NULL argument"); return GA_ERR_ARG; }
     if (n > ctx->cfg.max_batch_msgs) { set_error("ga_submit: %u messages exceed max_batch_msgs %u", n, ctx->cfg.max_batch_msgs); return GA_ERR_OVERFLOW; }
     std::lock_guard<std::mutex> lk(ctx->mu);
@@ -585,6 +588,7 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
     slot->release_to = release_to;
     *ticket = slot->ticket;
     return GA_OK;
+    GA_GUARD_END
 }
 
 // ---------------------------------------------------------------- regular tick batches
@@ -669,6 +673,7 @@ extern "C" int ga_submit_ticks(ga_ctx *ctx, uint64_t ring_offset, uint32_t n_tic
                                uint32_t chunk_bytes, const uint32_t *stream_ids, const uint8_t *flags,
                                uint64_t *ticket)
 {
+    GA_GUARD_BEGIN
     if (!ctx || !ticket || !stream_ids) { set_error("ga_submit_ticks: NULL argument"); return GA_ERR_ARG; }
     if (n_ticks == 0 || n_streams == 0) { set_error("ga_submit_ticks: empty batch"); return GA_ERR_ARG; }
     const uint64_t n64 = static_cast<uint64_t>(n_ticks) * n_streams;
@@ -832,6 +837,7 @@ extern "C" int ga_submit_ticks(ga_ctx *ctx, uint64_t ring_offset, uint32_t n_tic
     slot->release_to = ring_offset + span > tail ? ring_offset + span : tail;
     *ticket = slot->ticket;
     return GA_OK;
+    GA_GUARD_END
 }
 
 static Slot *find_ticket(ga_ctx *ctx, uint64_t ticket)
@@ -1083,6 +1089,7 @@ extern "C" int ga_arbitrate(ga_ctx *ctx, const uint32_t *seg_offsets, uint32_t n
                             const uint32_t *stream_ids, const uint8_t *status_in,
                             uint32_t *winner_idx, double *scores, uint8_t *status_out)
 {
+    GA_GUARD_BEGIN
     if (!ctx) { set_error("ga_arbitrate: NULL context"); return GA_ERR_ARG; }
     if (n_windows == 0) return GA_OK;
     if (!seg_offsets || !winner_idx) { set_error("ga_arbitrate: NULL argument"); return GA_ERR_ARG; }
@@ -1136,6 +1143,7 @@ extern "C" int ga_arbitrate(ga_ctx *ctx, const uint32_t *seg_offsets, uint32_t n
     }
     std::memcpy(winner_idx, hb + o_win, 4ull * n_windows);
     return GA_OK;
+    GA_GUARD_END
 }
 
 // ---------------------------------------------------------------- one-shot mirrors
@@ -1461,6 +1469,7 @@ extern "C" void ga_cluster_destroy(ga_cluster *cl)
 
 extern "C" int ga_cluster_create(ga_ctx *const *ctxs, uint32_t n_ctx, uint32_t max_guests, ga_cluster **out)
 {
+    GA_GUARD_BEGIN
     if (!ctxs || !out || n_ctx == 0 || n_ctx > 64) { set_error("ga_cluster_create: bad argument"); return GA_ERR_ARG; }
     *out = nullptr;
     for (uint32_t i = 0; i < n_ctx; i++) {
@@ -1512,6 +1521,7 @@ extern "C" int ga_cluster_create(ga_ctx *const *ctxs, uint32_t n_ctx, uint32_t m
     for (auto &s : cl->shards) { cudaSetDevice(s.dev); cudaDeviceSynchronize(); }
     *out = cl;
     return GA_OK;
+    GA_GUARD_END
 }
 
 extern "C" uint32_t ga_cluster_size(const ga_cluster *cl) { return cl ? static_cast<uint32_t>(cl->shards.size()) : 0u; }
@@ -1524,6 +1534,7 @@ extern "C" int ga_cluster_arbitrate(ga_cluster *cl, const uint32_t *seg_offsets,
                                     const uint32_t *shard_ids, const uint32_t *stream_ids, const uint8_t *status_in,
                                     uint32_t *winner_idx, double *scores, uint8_t *status_out)
 {
+    GA_GUARD_BEGIN
     if (!cl) { set_error("ga_cluster_arbitrate: NULL cluster"); return GA_ERR_ARG; }
     if (n_windows == 0) return GA_OK;
     if (!seg_offsets || !winner_idx) { set_error("ga_cluster_arbitrate: NULL argument"); return GA_ERR_ARG; }
@@ -1722,4 +1733,5 @@ extern "C" int ga_cluster_arbitrate(ga_cluster *cl, const uint32_t *seg_offsets,
         }
     }
     return GA_OK;
+    GA_GUARD_END
 }

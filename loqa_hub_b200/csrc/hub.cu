@@ -78,6 +78,7 @@ static Relay *find_relay(ga_hub *h, const char *id)
 
 extern "C" int ga_hub_create(ga_ctx *ctx, uint32_t max_streams, uint64_t window_duration_us, ga_hub **out)
 {
+    GA_GUARD_BEGIN
     // ctx may be NULL: the registry and the window bookkeeping then work on their own (that is how
     // the CPU-only tests run them); everything that needs samples reports GA_ERR_STATE
     if (!out || max_streams == 0) { set_error("ga_hub_create: bad argument"); return GA_ERR_ARG; }
@@ -89,12 +90,14 @@ extern "C" int ga_hub_create(ga_ctx *ctx, uint32_t max_streams, uint64_t window_
     if (window_duration_us) h->window_duration_us = window_duration_us;
     *out = h;
     return GA_OK;
+    GA_GUARD_END
 }
 
 // The hub over every GPU of the box: one context per GPU held by `cluster`.
 extern "C" int ga_hub_create_cluster(ga_cluster *cluster, uint32_t max_streams_per_shard, uint64_t window_duration_us,
                                      ga_hub **out)
 {
+    GA_GUARD_BEGIN
     if (!out || !cluster || max_streams_per_shard == 0) { set_error("ga_hub_create_cluster: bad argument"); return GA_ERR_ARG; }
     const uint32_t n = ga_cluster_size(cluster);
     ga_hub *h = new (std::nothrow) ga_hub;
@@ -106,6 +109,7 @@ extern "C" int ga_hub_create_cluster(ga_cluster *cluster, uint32_t max_streams_p
     if (window_duration_us) h->window_duration_us = window_duration_us;
     *out = h;
     return GA_OK;
+    GA_GUARD_END
 }
 
 extern "C" void ga_hub_destroy(ga_hub *h) { delete h; }
@@ -134,29 +138,35 @@ static int connect_relay(ga_hub *h, const char *relay_id, uint32_t group, uint32
 
 extern "C" int ga_hub_connect(ga_hub *h, const char *relay_id, uint32_t group, uint32_t *slot)
 {
+    GA_GUARD_BEGIN
     if (!h || !relay_id) { set_error("ga_hub_connect: bad argument"); return GA_ERR_ARG; }
     // a collision group lives on shard group % nGPU, so its windows normally stay on one GPU
     const uint32_t n = static_cast<uint32_t>(h->free_slots.size());
     return connect_relay(h, relay_id, group, group % n, slot);
+    GA_GUARD_END
 }
 
 // A relay whose audio has to live on a given GPU (it connected through another front end, or the
 // group's shard is full): its group's windows then span GPUs.
 extern "C" int ga_hub_connect_on(ga_hub *h, const char *relay_id, uint32_t group, uint32_t shard, uint32_t *slot)
 {
+    GA_GUARD_BEGIN
     if (!h || !relay_id) { set_error("ga_hub_connect_on: bad argument"); return GA_ERR_ARG; }
     if (shard >= h->free_slots.size()) { set_error("ga_hub_connect_on: shard %u of %zu", shard, h->free_slots.size()); return GA_ERR_ARG; }
     return connect_relay(h, relay_id, group, shard, slot);
+    GA_GUARD_END
 }
 
 extern "C" int ga_hub_relay_shard(ga_hub *h, const char *relay_id, uint32_t *shard)
 {
+    GA_GUARD_BEGIN
     if (!h || !relay_id || !shard) { set_error("ga_hub_relay_shard: bad argument"); return GA_ERR_ARG; }
     std::lock_guard<std::mutex> lk(h->mu);
     Relay *r = find_relay(h, relay_id);
     if (!r) { set_error("ga_hub_relay_shard: unknown relay %s", relay_id); return GA_ERR_STATE; }
     *shard = r->shard;
     return GA_OK;
+    GA_GUARD_END
 }
 
 // startArbitrationWindow :408-446.  Replaces the group's window pointer, adds the relay as the
@@ -199,6 +209,7 @@ static bool join_window(ga_hub *h, Relay *r, uint64_t now_us)
 
 extern "C" int ga_hub_start_window(ga_hub *h, const char *relay_id, uint64_t now_us, uint64_t *window_id)
 {
+    GA_GUARD_BEGIN
     if (!h || !relay_id) { set_error("ga_hub_start_window: bad argument"); return GA_ERR_ARG; }
     std::lock_guard<std::mutex> lk(h->mu);
     Relay *r = find_relay(h, relay_id);
@@ -206,16 +217,19 @@ extern "C" int ga_hub_start_window(ga_hub *h, const char *relay_id, uint64_t now
     const uint64_t id = start_window(h, r, now_us);
     if (window_id) *window_id = id;
     return GA_OK;
+    GA_GUARD_END
 }
 
 extern "C" int ga_hub_join_window(ga_hub *h, const char *relay_id, uint64_t now_us, int *joined)
 {
+    GA_GUARD_BEGIN
     if (!h || !relay_id || !joined) { set_error("ga_hub_join_window: bad argument"); return GA_ERR_ARG; }
     std::lock_guard<std::mutex> lk(h->mu);
     Relay *r = find_relay(h, relay_id);
     if (!r) { set_error("ga_hub_join_window: unknown relay %s", relay_id); return GA_ERR_STATE; }
     *joined = join_window(h, r, now_us) ? 1 : 0;
     return GA_OK;
+    GA_GUARD_END
 }
 
 // One received AudioChunk: the body of the StreamAudio loop, :939-1041.  keep_stream = 0 is the
@@ -223,6 +237,7 @@ extern "C" int ga_hub_join_window(ga_hub *h, const char *relay_id, uint64_t now_
 extern "C" int ga_hub_on_chunk(ga_hub *h, const char *relay_id, const uint8_t *audio, uint32_t nbytes,
                                int is_wake_word, int is_end_of_speech, uint64_t now_us, int *keep_stream)
 {
+    GA_GUARD_BEGIN
     if (!h || !relay_id || (nbytes && !audio)) { set_error("ga_hub_on_chunk: bad argument"); return GA_ERR_ARG; }
     std::lock_guard<std::mutex> lk(h->mu);
     Relay *r = find_relay(h, relay_id);
@@ -260,12 +275,14 @@ extern "C" int ga_hub_on_chunk(ga_hub *h, const char *relay_id, const uint8_t *a
         if (!active && keep_stream) *keep_stream = 0;             // :1018-1021
     }
     return GA_OK;
+    GA_GUARD_END
 }
 
 // The batch tick: everything pushed since the last flush goes through ONE ga_submit per GPU, all
 // GPUs working at the same time.
 extern "C" int ga_hub_flush(ga_hub *h, uint32_t *n_msgs)
 {
+    GA_GUARD_BEGIN
     if (!h) { set_error("ga_hub_flush: NULL hub"); return GA_ERR_ARG; }
     if (h->ctxs.empty()) { set_error("ga_hub_flush: this hub has no GPU context"); return GA_ERR_STATE; }
     struct Work {
@@ -331,6 +348,7 @@ extern "C" int ga_hub_flush(ga_hub *h, uint32_t *n_msgs)
     }
     if (n_msgs) *n_msgs = total - lost;
     return first_err;
+    GA_GUARD_END
 }
 
 // performArbitration :505-587 for a set of windows at once.
@@ -384,15 +402,18 @@ static int arbitrate_windows(ga_hub *h, const std::vector<uint64_t> &ids)
 
 extern "C" int ga_hub_perform_arbitration(ga_hub *h, uint64_t window_id)
 {
+    GA_GUARD_BEGIN
     if (!h) { set_error("ga_hub_perform_arbitration: NULL hub"); return GA_ERR_ARG; }
     std::lock_guard<std::mutex> lk(h->mu);
     if (h->windows.find(window_id) == h->windows.end()) { set_error("ga_hub_perform_arbitration: unknown window"); return GA_ERR_STATE; }
     return arbitrate_windows(h, {window_id});
+    GA_GUARD_END
 }
 
 // runArbitrationTimer :494-502 for all groups: arbitrate every active window whose duration elapsed.
 extern "C" int ga_hub_poll(ga_hub *h, uint64_t now_us, uint32_t *n_closed)
 {
+    GA_GUARD_BEGIN
     if (!h) { set_error("ga_hub_poll: NULL hub"); return GA_ERR_ARG; }
     std::lock_guard<std::mutex> lk(h->mu);
     std::vector<uint64_t> due;
@@ -400,11 +421,13 @@ extern "C" int ga_hub_poll(ga_hub *h, uint64_t now_us, uint32_t *n_closed)
         if (kv.second.is_active && now_us - kv.second.start_us >= kv.second.duration_us) due.push_back(kv.first);
     if (n_closed) *n_closed = static_cast<uint32_t>(due.size());
     return arbitrate_windows(h, due);
+    GA_GUARD_END
 }
 
 extern "C" int ga_hub_window_info(ga_hub *h, uint64_t window_id, int *is_active, char *winner_id, size_t winner_cap,
                                   uint32_t *n_relays)
 {
+    GA_GUARD_BEGIN
     if (!h) { set_error("ga_hub_window_info: NULL hub"); return GA_ERR_ARG; }
     std::lock_guard<std::mutex> lk(h->mu);
     auto it = h->windows.find(window_id);
@@ -416,21 +439,25 @@ extern "C" int ga_hub_window_info(ga_hub *h, uint64_t window_id, int *is_active,
         winner_id[winner_cap - 1] = 0;
     }
     return GA_OK;
+    GA_GUARD_END
 }
 
 // as.arbitrationWindow for a group: 0 = nil.
 extern "C" int ga_hub_active_window(ga_hub *h, uint32_t group, uint64_t *window_id)
 {
+    GA_GUARD_BEGIN
     if (!h || !window_id) { set_error("ga_hub_active_window: bad argument"); return GA_ERR_ARG; }
     std::lock_guard<std::mutex> lk(h->mu);
     auto gw = h->group_window.find(group);
     *window_id = gw == h->group_window.end() ? 0 : gw->second;
     return GA_OK;
+    GA_GUARD_END
 }
 
 extern "C" int ga_hub_relay_info(ga_hub *h, const char *relay_id, int *status, double *signal_strength,
                                  int *cancel_closed, uint32_t *slot)
 {
+    GA_GUARD_BEGIN
     if (!h || !relay_id) { set_error("ga_hub_relay_info: bad argument"); return GA_ERR_ARG; }
     std::lock_guard<std::mutex> lk(h->mu);
     Relay *r = find_relay(h, relay_id);
@@ -440,22 +467,26 @@ extern "C" int ga_hub_relay_info(ga_hub *h, const char *relay_id, int *status, d
     if (cancel_closed) *cancel_closed = r->cancel_closed ? 1 : 0;
     if (slot) *slot = r->slot;
     return GA_OK;
+    GA_GUARD_END
 }
 
 // isRelayActive :880-913: 1 / 0; a relay that is not in activeStreams is inactive (:884-888).
 extern "C" int ga_hub_is_relay_active(ga_hub *h, const char *relay_id)
 {
+    GA_GUARD_BEGIN
     if (!h || !relay_id) return 0;
     std::lock_guard<std::mutex> lk(h->mu);
     Relay *r = find_relay(h, relay_id);
     if (!r || !r->in_active_streams) return 0;
     return (r->status == GA_RELAY_WINNER || r->status == GA_RELAY_CONNECTED || r->status == GA_RELAY_CONTENDING) ? 1 : 0;
+    GA_GUARD_END
 }
 
 // What the reference's tests do by writing the map directly (collision_detection_test.go:195-216,
 // :361-369): put a relay into activeStreams with a given status.
 extern "C" int ga_hub_set_relay_status(ga_hub *h, const char *relay_id, int status)
 {
+    GA_GUARD_BEGIN
     if (!h || !relay_id || status < GA_RELAY_CONNECTED || status > GA_RELAY_CANCELLED) { set_error("ga_hub_set_relay_status: bad argument"); return GA_ERR_ARG; }
     std::lock_guard<std::mutex> lk(h->mu);
     Relay *r = find_relay(h, relay_id);
@@ -463,12 +494,14 @@ extern "C" int ga_hub_set_relay_status(ga_hub *h, const char *relay_id, int stat
     r->status = status;
     r->in_active_streams = true;
     return GA_OK;
+    GA_GUARD_END
 }
 
 // Request completion as the reference's tests spell it (collision_detection_test.go:361-369):
 // drop the group's window if this relay won it, and return the relay to Connected.
 extern "C" int ga_hub_complete_request(ga_hub *h, const char *relay_id)
 {
+    GA_GUARD_BEGIN
     if (!h || !relay_id) { set_error("ga_hub_complete_request: bad argument"); return GA_ERR_ARG; }
     std::lock_guard<std::mutex> lk(h->mu);
     Relay *r = find_relay(h, relay_id);
@@ -477,11 +510,13 @@ extern "C" int ga_hub_complete_request(ga_hub *h, const char *relay_id)
     if (gw != h->group_window.end() && h->windows[gw->second].winner == r->id) h->group_window.erase(gw);
     r->status = GA_RELAY_CONNECTED;
     return GA_OK;
+    GA_GUARD_END
 }
 
 // cleanupRelay :916-923: remove from activeStreams; the stream slot and its GPU buffers are freed.
 extern "C" int ga_hub_cleanup_relay(ga_hub *h, const char *relay_id)
 {
+    GA_GUARD_BEGIN
     if (!h || !relay_id) { set_error("ga_hub_cleanup_relay: bad argument"); return GA_ERR_ARG; }
     std::lock_guard<std::mutex> lk(h->mu);
     auto it = h->relays.find(relay_id);
@@ -490,16 +525,19 @@ extern "C" int ga_hub_cleanup_relay(ga_hub *h, const char *relay_id)
     h->relays.erase(it);
     h->free_slots[shard].push_back(slot);
     return h->ctxs.empty() ? GA_OK : ga_stream_reset(h->ctxs[shard], slot);
+    GA_GUARD_END
 }
 
 extern "C" int ga_hub_active_streams(ga_hub *h, uint32_t *n)
 {
+    GA_GUARD_BEGIN
     if (!h || !n) { set_error("ga_hub_active_streams: bad argument"); return GA_ERR_ARG; }
     std::lock_guard<std::mutex> lk(h->mu);
     uint32_t c = 0;
     for (auto &kv : h->relays) c += kv.second.in_active_streams ? 1u : 0u;
     *n = c;
     return GA_OK;
+    GA_GUARD_END
 }
 
 // ---------------------------------------------------------------- f32 -> WAV for the winner
@@ -509,6 +547,7 @@ extern "C" int ga_hub_active_streams(ga_hub *h, uint32_t *n)
 // region) straight into the caller's buffer behind the header — no per-sample allocation (:391-396).
 extern "C" int ga_fetch_wav(ga_ctx *ctx, uint32_t stream_id, uint32_t sample_rate, uint8_t *out, size_t cap, size_t *n_bytes)
 {
+    GA_GUARD_BEGIN
     if (!ctx || !n_bytes) { set_error("ga_fetch_wav: bad argument"); return GA_ERR_ARG; }
     uint64_t n = 0, wake = 0;
     int rc = ga_stream_info(ctx, stream_id, &n, &wake);
@@ -526,11 +565,13 @@ extern "C" int ga_fetch_wav(ga_ctx *ctx, uint32_t stream_id, uint32_t sample_rat
     std::memcpy(out + 36, "data", 4);  le32(out + 40, static_cast<uint32_t>(data_size));  // :387-388
     if (n == 0) return GA_OK;
     return ga_fetch_samples(ctx, stream_id, 0, n, reinterpret_cast<float *>(out + 44));
+    GA_GUARD_END
 }
 
 // The winner's audio as the STT request body, from whichever GPU holds it.
 extern "C" int ga_hub_fetch_wav(ga_hub *h, const char *relay_id, uint32_t sample_rate, uint8_t *out, size_t cap, size_t *n_bytes)
 {
+    GA_GUARD_BEGIN
     if (!h || !relay_id) { set_error("ga_hub_fetch_wav: bad argument"); return GA_ERR_ARG; }
     ga_ctx *ctx = nullptr;
     uint32_t slot = 0;
@@ -542,4 +583,5 @@ extern "C" int ga_hub_fetch_wav(ga_hub *h, const char *relay_id, uint32_t sample
         ctx = h->ctxs[r->shard]; slot = r->slot;
     }
     return ga_fetch_wav(ctx, slot, sample_rate, out, cap, n_bytes);
+    GA_GUARD_END
 }
