@@ -365,7 +365,14 @@ static int arbitrate_windows(ga_hub *h, const std::vector<uint64_t> &ids)
         if (it == h->windows.end() || !it->second.is_active) continue;    // :508-511 already arbitrated
         Window &w = it->second;
         for (auto &rid : w.relays) {
-            Relay &r = h->relays[rid];
+            auto rit = h->relays.find(rid);
+            if (rit == h->relays.end()) {
+                // the relay was cleaned up (cleanupRelay :916-923) while its window was open: its stream
+                // slot is gone, so it takes part as a member that is not contending
+                sid.push_back(0); shard.push_back(0); st_in.push_back(GA_RELAY_CANCELLED); scores.push_back(0.0);
+                continue;
+            }
+            Relay &r = rit->second;
             sid.push_back(r.slot);
             shard.push_back(r.shard);
             st_in.push_back(static_cast<uint8_t>(r.status));
@@ -387,7 +394,9 @@ static int arbitrate_windows(ga_hub *h, const std::vector<uint64_t> &ids)
     for (size_t k = 0; k < ws.size(); k++) {
         Window &w = *ws[k];
         for (uint32_t m = seg[k]; m < seg[k + 1]; m++) {
-            Relay &r = h->relays[w.relays[m - seg[k]]];
+            auto rit = h->relays.find(w.relays[m - seg[k]]);
+            if (rit == h->relays.end()) continue;                         // cleaned up meanwhile: nothing to update
+            Relay &r = rit->second;
             r.signal_strength = scores[m];                                // :528
             r.status = st_out[m];                                         // :553-571
             if (st_out[m] == GA_RELAY_CANCELLED) r.cancel_closed = true;  // :561 close(relay.CancelChannel)

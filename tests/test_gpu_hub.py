@@ -268,3 +268,25 @@ def test_two_utterances_of_one_relay_inside_one_tick(svc):
     want_other = np.concatenate([ora.bytes_to_float32(c)[0] for c in first])
     assert np.array_equal(svc.ctx.fetch_samples(svc.relay(other).slot), want_other)
     assert svc.flush() == 0
+
+
+def test_relay_cleaned_up_while_its_window_is_open(svc):
+    """cleanupRelay (:916-923) can run while the relay's window is still open (its gRPC stream
+    ended).  Its audio is gone with its stream slot, so it no longer contends; the window closes
+    for the others, and no ghost relay appears in the registry."""
+    for r in ("a", "b", "c"):
+        svc.connect(r)
+    loud, quiet = pcm(np.full(320, 20000)), pcm(np.full(320, 3000))
+    assert svc.on_chunk("a", loud, True, False, 0)
+    assert svc.on_chunk("b", quiet, True, False, 1 * MS)
+    assert svc.on_chunk("c", quiet, True, False, 2 * MS)
+    svc.flush()
+    window = svc.arbitration_window()
+    svc.cleanup_relay("a")                               # the loudest relay hangs up
+    assert svc.active_streams() == 2
+    assert svc.poll(now_us=200 * MS) == 1
+    assert svc.window(window).winner_id == "b"           # first of the two equals that are left
+    assert svc.relay("b").status == RelayStatusWinner and svc.relay("c").status == RelayStatusCancelled
+    assert svc.active_streams() == 2
+    with pytest.raises(L.GpuAudioError):
+        svc.relay("a")                                   # not resurrected by the arbitration
