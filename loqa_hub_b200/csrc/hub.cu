@@ -14,6 +14,7 @@
 // rooms arbitrate concurrently.  With a single group the behaviour is the reference's.
 // Time is injected (now_us) instead of read from a clock, and the timer goroutine (:494-502) is
 // ga_hub_poll: every window whose duration has elapsed is arbitrated in ONE ga_arbitrate call.
+#include <algorithm>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -533,6 +534,10 @@ extern "C" int ga_hub_cleanup_relay(ga_hub *h, const char *relay_id)
     const uint32_t slot = it->second.slot, shard = it->second.shard;
     h->relays.erase(it);
     h->free_slots[shard].push_back(slot);
+    // chunks of the relay that were not flushed yet go with it: the slot may get a new owner before
+    // the next tick (their ring space is released with the next ticket that is waited)
+    auto &q = h->pending[shard];
+    q.erase(std::remove_if(q.begin(), q.end(), [slot](const ga_msg &m) { return m.stream_id == slot; }), q.end());
     return h->ctxs.empty() ? GA_OK : ga_stream_reset(h->ctxs[shard], slot);
     GA_GUARD_END
 }

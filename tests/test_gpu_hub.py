@@ -290,3 +290,19 @@ def test_relay_cleaned_up_while_its_window_is_open(svc):
     assert svc.active_streams() == 2
     with pytest.raises(L.GpuAudioError):
         svc.relay("a")                                   # not resurrected by the arbitration
+
+
+def test_cleanup_drops_the_relays_unflushed_chunks(svc):
+    """A relay that disconnects before the batching tick: its queued chunks must not end up in the
+    stream of the relay that inherits its slot."""
+    svc.connect("old")
+    slot = svc.relay("old").slot
+    assert svc.on_chunk("old", pcm(np.full(320, 11111)), True, False, 0)
+    svc.cleanup_relay("old")
+    svc.connect("new", group=5)
+    assert svc.relay("new").slot == slot                 # the freed slot is handed out again
+    mine = pcm(np.full(320, -222))
+    assert svc.on_chunk("new", mine, True, False, 1 * MS)
+    assert svc.flush() == 1
+    assert np.array_equal(svc.ctx.fetch_samples(slot), ora.bytes_to_float32(mine)[0])
+    svc.ctx.push(b"\0" * 16)                             # the ring keeps working past the skipped reservation
