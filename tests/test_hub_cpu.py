@@ -72,3 +72,28 @@ def test_anything_that_needs_samples_refuses_without_a_gpu_context(svc):
             call()
         assert e.value.code == L.GA_ERR_STATE
     assert svc.poll(10 * MS) == 0                                  # nothing due yet: no GPU needed
+
+
+def test_slot_bookkeeping_and_shard_placement_without_a_gpu(svc):
+    """Stream slots are handed out densely, freed by cleanupRelay and reused; a hub over one context
+    (or none) has a single shard, so ga_hub_connect_on accepts shard 0 only."""
+    slots = [svc.connect("r%d" % i, group=i) for i in range(8)]
+    assert slots == list(range(8))
+    with pytest.raises(L.GpuAudioError) as e:
+        svc.connect("one-too-many")
+    assert e.value.code == L.GA_ERR_OVERFLOW
+    svc.cleanup_relay("r3")
+    assert svc.connect("again") == 3                                 # the freed slot
+    assert svc.connect("r5", group=9) == 5                           # a known relay keeps its slot
+    assert svc.relay_shard("r5") == 0
+    svc.cleanup_relay("r0")
+    assert svc.connect_on("pinned", 4, 0) == 0
+    with pytest.raises(L.GpuAudioError) as e:
+        svc.connect_on("elsewhere", 4, 1)
+    assert e.value.code == L.GA_ERR_ARG
+    with pytest.raises(L.GpuAudioError) as e:
+        svc.relay_shard("nobody")
+    assert e.value.code == L.GA_ERR_STATE
+    with pytest.raises(L.GpuAudioError) as e:
+        svc.fetch_wav("r5")
+    assert e.value.code == L.GA_ERR_STATE                            # needs samples -> needs a GPU context
