@@ -130,6 +130,24 @@ __device__ __forceinline__ float pcm_to_f32(float v)
 
 __device__ __forceinline__ float pcm_to_f32(int v) { return pcm_to_f32(static_cast<float>(v)); }
 
+// Two samples per instruction: Blackwell's packed FP32 forms (FMUL2 / FFMA2) perform two
+// independent IEEE operations, so the result is bit-identical to two scalar calls; it halves the
+// issue slots of the conversion.  sq0/sq1 receive the squares (f32-rounded, audio_service.go:828).
+__device__ __forceinline__ void pcm_to_f32x2(float v0, float v1, float &x0, float &x1, float &sq0, float &sq1)
+{
+    const float r = 1.0f / 32767.0f;
+    unsigned long long v, rr, nn, q0, e, q, sq;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(v) : "f"(v0), "f"(v1));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(rr) : "f"(r));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(nn) : "f"(-32767.0f));
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(q0) : "l"(v), "l"(rr));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(e) : "l"(nn), "l"(q0), "l"(v));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(q) : "l"(e), "l"(rr), "l"(q0));
+    asm("mul.rn.f32x2 %0, %1, %1;" : "=l"(sq) : "l"(q));
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(x0), "=f"(x1) : "l"(q));
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(sq0), "=f"(sq1) : "l"(sq));
+}
+
 // float64(sample*sample): product rounded to f32 first, then widened (audio_service.go:828)
 __device__ __forceinline__ double sq_f64(float s) { return static_cast<double>(__fmul_rn(s, s)); }
 

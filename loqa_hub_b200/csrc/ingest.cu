@@ -78,6 +78,9 @@ struct IngestParams {
 #ifndef GA_SCHED_IMAD
 #define GA_SCHED_IMAD true
 #endif
+#ifndef GA_PACKED_CONVERT
+#define GA_PACKED_CONVERT 1
+#endif
 #ifndef GA_SHA_ROLLED
 #define GA_SHA_ROLLED true
 #endif
@@ -338,8 +341,14 @@ ingest_kernel(const IngestParams p, const __grid_constant__ CUtensorMap tmap)
                                 float v0, v1, v2, v3;
                                 unpack2<kSha && GA_XU_UNPACK>(w[j], v0, v1);
                                 unpack2<kSha && GA_XU_UNPACK>(w[j + 1], v2, v3);
+#if GA_PACKED_CONVERT
+                                float x0, x1, x2, x3, q0_, q1_, q2_, q3_;
+                                pcm_to_f32x2(v0, v1, x0, x1, q0_, q1_);
+                                pcm_to_f32x2(v2, v3, x2, x3, q2_, q3_);
+#else
                                 const float x0 = pcm_to_f32(v0), x1 = pcm_to_f32(v1);
                                 const float x2 = pcm_to_f32(v2), x3 = pcm_to_f32(v3);
+#endif
                                 if (kCoop) {
                                     *reinterpret_cast<float4 *>(orow + b * 32 + 2 * j) = make_float4(x0, x1, x2, x3);
                                 } else if (kLaneStore) {
@@ -347,8 +356,12 @@ ingest_kernel(const IngestParams p, const __grid_constant__ CUtensorMap tmap)
                                     else { g[2 * j] = x0; g[2 * j + 1] = x1; g[2 * j + 2] = x2; g[2 * j + 3] = x3; }
                                 }
                                 if (kFeat) {
+#if GA_PACKED_CONVERT
+                                    sqf[2 * j] = q0_; sqf[2 * j + 1] = q1_; sqf[2 * j + 2] = q2_; sqf[2 * j + 3] = q3_;
+#else
                                     sqf[2 * j] = __fmul_rn(x0, x0); sqf[2 * j + 1] = __fmul_rn(x1, x1);
                                     sqf[2 * j + 2] = __fmul_rn(x2, x2); sqf[2 * j + 3] = __fmul_rn(x3, x3);
+#endif
                                     frm.minmax_word(w[j]);
                                     frm.minmax_word(w[j + 1]);
                                     frm.count_nonzero(sqf[2 * j], sqf[2 * j + 1], sqf[2 * j + 2], sqf[2 * j + 3]);
