@@ -44,13 +44,33 @@ constexpr int kRsWarpBytes = 2 * kPcmStage + kMonoFloats * 4 + kYFloats * 4 + 64
 
 __constant__ uint32_t c_tap_bits[kTaps] = GA_RESAMPLE_TAP_BITS;
 
+#ifndef GA_PACKED_MONO
+#define GA_PACKED_MONO 1
+#endif
 __device__ __forceinline__ float mono_of(uint32_t lr)
 {
     // lr = one interleaved stereo frame: L in the low half, R in the high half
     const uint32_t x = lr ^ 0x80008000u;
+#if GA_PACKED_MONO
+    // both channels per instruction (FADD2 / FMUL2 / FFMA2: two independent IEEE operations each)
+    const float rcp = 1.0f / 32767.0f;
+    unsigned long long v, q0, e, q, kb, kr, kn;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(v) : "r"(__byte_perm(x, 0x4B000000u, 0x7610)), "r"(__byte_perm(x, 0x4B000000u, 0x7632)));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(kb) : "f"(-8421376.0f));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(kr) : "f"(rcp));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(kn) : "f"(-32767.0f));
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(v) : "l"(v), "l"(kb));
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(q0) : "l"(v), "l"(kr));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(e) : "l"(kn), "l"(q0), "l"(v));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(q) : "l"(e), "l"(kr), "l"(q0));
+    float l, r;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(l), "=f"(r) : "l"(q));
+    return __fmul_rn(__fadd_rn(l, r), 0.5f);
+#else
     const float l = __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7610)) - 8421376.0f;
     const float r = __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7632)) - 8421376.0f;
     return __fmul_rn(__fadd_rn(pcm_to_f32(l), pcm_to_f32(r)), 0.5f);
+#endif
 }
 
 // number of outputs of a message of nfr frames that starts at absolute frame n0, and the mono[]
