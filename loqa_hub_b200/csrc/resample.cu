@@ -41,6 +41,20 @@ constexpr int kMonoFloats = ((kPad + kRsMaxFrames + 36 + 3) / 4) * 4 + 96;
 constexpr int kYFloats = ((kRsMaxOut + 3) / 4) * 4 + 4;
 constexpr int kPcmStage = kRsMaxFrames * 4 + 16;
 constexpr int kRsWarpBytes = 2 * kPcmStage + kMonoFloats * 4 + kYFloats * 4 + 64;
+// pass 2 staging: slices of 32 outputs of the group's 32 messages, rows padded by 16 B (conflict-free
+// lane-per-row LDS.128), two buffers laid over the PCM stages and mono[] that pass 1 is done with
+constexpr int kP2Slice = 32;
+constexpr int kP2RowStride = kP2Slice * 4 + 16;
+constexpr int kP2BufBytes = 32 * kP2RowStride;
+static_assert(2 * kP2BufBytes <= 2 * kPcmStage + kMonoFloats * 4, "pass-2 buffers must fit the pass-1 buffers");
+
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 __constant__ uint32_t c_tap_bits[kTaps] = GA_RESAMPLE_TAP_BITS;
 
@@ -257,11 +271,12 @@ resample48_kernel(const ResampleParams p)
 
         // ---------------- pass 2: lane = message.  calculateSignalStrength (audio_service.go:818-852)
         // over the message's outputs: the float64 sum strictly in index order, non-zero count, peak.
-        if (static_cast<uint32_t>(lane) < cnt) {
+        {
+            const bool mine = static_cast<uint32_t>(lane) < cnt;
             const uint32_t mi = base + lane;
             const ga_rdesc &d = dl;
             const uint32_t nfr = min(d.nbytes >> 2, static_cast<uint32_t>(kRsMaxFrames));
-            const uint32_t n_out = out_count(d.n0, nfr, nullptr);
+            const uint32_t n_out = mine ? out_count(d.n0, nfr, nullptr) : 0u;
             const float *y = p.samples + d.out_off;
             double msg_sum = 0.0, frm_sum = 0.0;
             uint32_t nz = 0, fnz = 0, fn = 0, fidx = 0;
@@ -284,24 +299,76 @@ resample48_kernel(const ResampleParams p)
                     }
                 }
             };
-            uint32_t k = 0;
-            if ((d.out_off & 3ull) == 0) {
-                for (; k + 4 <= n_out; k += 4) {
-                    const float4 t = __ldcg(reinterpret_cast<const float4 *>(y + k));
-                    step(t.x); step(t.y); step(t.z); step(t.w);
+            // The outputs were written cooperatively in pass 1 and are read back per lane here.  Each
+            // lane reading its own row from L2 exposes the full memory latency once per 16 bytes, so
+            // the rows come back through shared memory instead: slices of 32 samples of all 32 messages,
+            // fetched by asynchronous copies (cp.async: coalesced, no registers, two slices in flight)
+            // into the buffers pass 1 no longer needs.
+            const uint32_t max_out = __reduce_max_sync(FULL, n_out);
+            const bool staged = __all_sync(FULL, !mine || (d.out_off & 3ull) == 0) && max_out >= kP2Slice;
+            if (staged) {
+                const uint32_t n_slices = (max_out + kP2Slice - 1) / kP2Slice;
+                auto issue_slice = [&](uint32_t sl) {
+                    uint8_t *buf = wbase + (sl & 1u) * kP2BufBytes;
+#pragma unroll
+                    for (int i = 0; i < 8; i++) {
+                        const int msg_i = i * 4 + (lane >> 3), piece = lane & 7;
+                        const uint64_t off_m = __shfl_sync(FULL, d.out_off, msg_i);
+                        const uint32_t n_m = __shfl_sync(FULL, n_out, msg_i);
+                        const uint32_t s0 = sl * kP2Slice + piece * 4;
+                        if (s0 < n_m)
+                            cp_async16(buf + msg_i * kP2RowStride + piece * 16, p.samples + off_m + s0);
+                    }
+                    cp_async_commit();
+                };
+                issue_slice(0);
+                if (n_slices > 1) issue_slice(1);
+                for (uint32_t sl = 0; sl < n_slices; sl++) {
+                    if (sl + 1 < n_slices) cp_async_wait<1>(); else cp_async_wait<0>();
+                    __syncwarp();
+                    const uint32_t lo = sl * kP2Slice;
+                    if (lo < n_out) {
+                        const uint32_t c = min(n_out - lo, static_cast<uint32_t>(kP2Slice));
+                        const float4 *row = reinterpret_cast<const float4 *>(wbase + (sl & 1u) * kP2BufBytes + lane * kP2RowStride);
+                        uint32_t k = 0;
+                        for (; k + 4 <= c; k += 4) {
+                            const float4 t = row[k >> 2];
+                            step(t.x); step(t.y); step(t.z); step(t.w);
+                        }
+                        if (k < c) {
+                            const float4 t = row[k >> 2];
+                            step(t.x);
+                            if (k + 1 < c) step(t.y);
+                            if (k + 2 < c) step(t.z);
+                        }
+                    }
+                    __syncwarp();
+                    if (sl + 2 < n_slices) issue_slice(sl + 2);
                 }
+                // the next group's PCM arrives in these buffers through the TMA (async proxy)
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            } else if (mine) {
+                uint32_t k = 0;
+                if ((d.out_off & 3ull) == 0) {
+                    for (; k + 4 <= n_out; k += 4) {
+                        const float4 t = __ldcg(reinterpret_cast<const float4 *>(y + k));
+                        step(t.x); step(t.y); step(t.z); step(t.w);
+                    }
+                }
+                for (; k < n_out; k++) step(__ldcg(y + k));
             }
-            for (; k < n_out; k++) step(__ldcg(y + k));
-            if (p.frames && fn) {
-                ga_frame f;
-                f.sumsq = frm_sum; f.rms = __dsqrt_rn(__ddiv_rn(frm_sum, static_cast<double>(fn)));
-                f.n_samples = fn; f.nonzero = fnz; f.peak = fpk; f.vad = f.rms > p.vad ? 1u : 0u;
-                p.frames[static_cast<uint64_t>(d.frame_off) + fidx] = f;
+            if (mine) {
+                if (p.frames && fn) {
+                    ga_frame f;
+                    f.sumsq = frm_sum; f.rms = __dsqrt_rn(__ddiv_rn(frm_sum, static_cast<double>(fn)));
+                    f.n_samples = fn; f.nonzero = fnz; f.peak = fpk; f.vad = f.rms > p.vad ? 1u : 0u;
+                    p.frames[static_cast<uint64_t>(d.frame_off) + fidx] = f;
+                }
+                ga_result *r = p.results + mi;
+                const double rms = n_out ? __dsqrt_rn(__ddiv_rn(msg_sum, static_cast<double>(n_out))) : 0.0;
+                r->sumsq = msg_sum; r->rms = rms; r->n_samples = n_out; r->nonzero = nz; r->peak = pk;
+                r->flags = (d.flags << 8) | (rms > p.vad ? 1u : 0u);
             }
-            ga_result *r = p.results + mi;
-            const double rms = n_out ? __dsqrt_rn(__ddiv_rn(msg_sum, static_cast<double>(n_out))) : 0.0;
-            r->sumsq = msg_sum; r->rms = rms; r->n_samples = n_out; r->nonzero = nz; r->peak = pk;
-            r->flags = (d.flags << 8) | (rms > p.vad ? 1u : 0u);
         }
         __syncwarp();
     }
