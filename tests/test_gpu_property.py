@@ -54,7 +54,7 @@ def payload(kind, n, seed):
 batches = st.lists(st.tuples(lengths, kinds, st.integers(0, N_STREAMS - 1), st.booleans()), min_size=1, max_size=48)
 
 
-@settings(max_examples=200, deadline=None, derandomize=True,
+@settings(max_examples=200, deadline=None, derandomize=True, database=None,
           suppress_health_check=[HealthCheck.too_slow, HealthCheck.data_too_large])
 @given(batch=batches, uniform_len=st.one_of(st.none(), st.sampled_from([2, 64, 640, 642, 1000])),
        mode=st.sampled_from([L.DO_ALL, L.DO_CONVERT | L.DO_FEATURES, L.DO_SHA256, L.DO_SHA256 | L.DO_FEATURES,
@@ -111,7 +111,7 @@ chunk48 = st.one_of(st.integers(0, 40), st.integers(180, 200), st.just(3840), st
                     st.sampled_from([4 * 46, 4 * 47, 4 * 48, 4 * 959 + 1, 3839]))
 
 
-@settings(max_examples=150, deadline=None, derandomize=True,
+@settings(max_examples=150, deadline=None, derandomize=True, database=None,
           suppress_health_check=[HealthCheck.too_slow, HealthCheck.data_too_large])
 @given(plan=st.lists(st.tuples(st.integers(0, 3), chunk48, st.booleans()), min_size=1, max_size=40),
        seed=st.integers(0, 2 ** 31))
@@ -181,7 +181,7 @@ member = st.tuples(st.integers(0, 2600), st.sampled_from(["random", "zeros", "ma
                    st.sampled_from([L.RELAY_CONTENDING] * 4 + [L.RELAY_CONNECTED, L.RELAY_WINNER, L.RELAY_CANCELLED]))
 
 
-@settings(max_examples=120, deadline=None, derandomize=True,
+@settings(max_examples=120, deadline=None, derandomize=True, database=None,
           suppress_health_check=[HealthCheck.too_slow, HealthCheck.data_too_large])
 @given(windows=st.lists(st.lists(member, min_size=0, max_size=9), min_size=1, max_size=7), seed=st.integers(0, 2 ** 31),
        twin=st.booleans())
@@ -227,7 +227,7 @@ def test_any_set_of_windows_arbitrates_like_the_reference(windows, seed, twin):
 _pairs = {}
 
 
-@settings(max_examples=80, deadline=None, derandomize=True,
+@settings(max_examples=80, deadline=None, derandomize=True, database=None,
           suppress_health_check=[HealthCheck.too_slow, HealthCheck.data_too_large])
 @given(fmt48=st.booleans(), utter=st.booleans(), n_streams=st.integers(1, 12),
        ticks=st.lists(st.integers(1, 5), min_size=1, max_size=3), wake_ticks=st.integers(0, 3),
