@@ -389,6 +389,13 @@ def main():
     expect = plan.seg_offsets[:-1].astype(np.int64)      # relay 0 has the highest gain in every group
     if not np.array_equal(win, expect):
         raise SystemExit("bench: arbitration winners are wrong on rank %d" % rank)
+    if fmt48:           # a digest of the resident run against hashlib (message 0 and the last one)
+        import hashlib
+        rec = results.view(torch.uint8).reshape(n_msgs, 64)
+        for mchk in (0, n_msgs - 1):
+            raw = pcm.view(torch.uint8)[mchk * msg_bytes:(mchk + 1) * msg_bytes].cpu().numpy().tobytes()
+            if rec[mchk, :32].cpu().numpy().tobytes() != hashlib.sha256(raw).digest():
+                raise SystemExit("bench: 48 kHz digest of message %d is wrong on rank %d" % (mchk, rank))
     if exchange is not None and exchange.error_flag():
         raise SystemExit("bench: cross-shard exchange timed out on rank %d" % rank)
     if world > 1:
