@@ -207,7 +207,11 @@ typedef struct ga_rdesc {
  * in fixed order with fused multiply-adds, on the stream's absolute frame timeline; then
  * results[i].{sumsq,rms,n_samples,nonzero,peak,flags} (and frames) over y as in ga_k_ingest.
  * The digest field of results[i] is not written (run ga_k_ingest with GA_DO_SHA256 on the same
- * slab for the fingerprint of the received bytes).  d_hist_state: 192 bytes per stream. */
+ * slab for the fingerprint of the received bytes).  d_hist_state: 192 bytes per stream (NULL: nothing
+ * is carried).  At most ONE message per stream and call may carry GA_RS_SAVE_HIST — the stream's last;
+ * the saves run as a second small launch behind the decimator on `stream`, so that a stream's first
+ * message of the call (GA_HIST_STATE) reads the state the PREVIOUS call left, wherever in the batch
+ * the two messages sit. */
 int ga_k_resample48(const void *d_pcm, const ga_rdesc *d_desc, uint32_t n_msgs, void *d_hist_state,
                     float *d_samples, ga_result *d_results, ga_frame *d_frames,
                     double vad_threshold, void *stream);

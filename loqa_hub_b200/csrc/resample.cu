@@ -247,25 +247,9 @@ resample48_kernel(const ResampleParams p)
                 for (uint32_t k = lane; k < n_out; k += 32) out[k] = ybuf[k];
             }
 
-            // carry: the stream's last 47 raw frames, for the first message of the next batch
-            if ((d.flags & GA_RS_SAVE_HIST) && p.hist_state) {
-                uint32_t *hs = reinterpret_cast<uint32_t *>(p.hist_state + static_cast<uint64_t>(d.stream_id) * 192);
-                const uint32_t *mw = reinterpret_cast<const uint32_t *>(msg);
-                uint32_t v[2] = {0u, 0u};
-#pragma unroll
-                for (int t = 0; t < 2; t++) {
-                    const int j = lane + 32 * t;
-                    // frame (nfr - 47 + j) of this message, or — for a short message — of the history before it
-                    const int64_t a = static_cast<int64_t>(nfr) - kHist + j;
-                    if (j < kHist) v[t] = a >= 0 ? mw[a] : (hsrc ? hsrc[kHist + a] : 0u);
-                }
-                __syncwarp();          // all reads of the old state are done before it is overwritten
-#pragma unroll
-                for (int t = 0; t < 2; t++) {
-                    const int j = lane + 32 * t;
-                    if (j < kHist) hs[j] = v[t];
-                }
-            }
+            // (the carry of the stream's last 47 raw frames into hist_state is NOT done here: another
+            // warp of this launch may still have to read the stream's OLD state for an earlier chunk of
+            // the batch — resample48_save_hist_kernel runs behind this launch on the same stream)
             __syncwarp();              // mono / ybuf / this PCM stage are free again
         }
 
@@ -374,6 +358,64 @@ resample48_kernel(const ResampleParams p)
     }
 }
 
+
+// Carry of the per-stream filter history to the next batch: for every message flagged
+// GA_RS_SAVE_HIST (the context flags the stream's LAST chunk of the batch), the 47 stereo frames
+// that precede the end of the message go to hist_state[stream_id].  This runs as its own launch
+// BEHIND resample48_kernel on the same CUDA stream: inside the main kernel the save of a stream's
+// last chunk raced with the GA_HIST_STATE read of the same stream's first chunk of the batch when
+// the two sat in different 32-message groups (different warps, no ordering).  Here a stream's old
+// state is read (short last chunk: its history is part of the new state) and overwritten by ONE
+// warp with a __syncwarp between, and nothing else reads hist_state during this launch.
+// A warp scans 32 descriptors, then handles its flagged messages one at a time.
+constexpr int kSaveWarps = 8;
+__global__ void __launch_bounds__(kSaveWarps * 32)
+resample48_save_hist_kernel(const uint8_t *__restrict__ pcm, const ga_rdesc *__restrict__ desc, uint8_t *hist_state,
+                            uint32_t n_msgs)
+{
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t base = (blockIdx.x * kSaveWarps + (threadIdx.x >> 5)) * 32u;
+    if (base >= n_msgs) return;
+    constexpr uint32_t FULL = 0xffffffffu;
+    const uint32_t mi = base + lane;
+    uint4 tail = make_uint4(0u, 0u, 0u, 0u);               // {nbytes, stream_id, flags, frame_off}
+    if (mi < n_msgs) tail = __ldg(reinterpret_cast<const uint4 *>(desc + mi) + 2);
+    uint32_t todo = __ballot_sync(FULL, (tail.z & GA_RS_SAVE_HIST) != 0u);
+    uint64_t in_off = 0, hist_off = 0;
+    uint32_t hist_kind = GA_HIST_ZERO;
+    if (todo >> lane & 1u) {
+        in_off = desc[mi].in_off;
+        hist_off = desc[mi].hist_off;
+        hist_kind = desc[mi].hist_kind;
+    }
+    while (todo) {
+        const int i = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const uint64_t m_in = __shfl_sync(FULL, in_off, i), m_hist = __shfl_sync(FULL, hist_off, i);
+        const uint32_t kind = __shfl_sync(FULL, hist_kind, i), nb = __shfl_sync(FULL, tail.x, i), sid = __shfl_sync(FULL, tail.y, i);
+        const uint32_t nfr = min(nb >> 2, static_cast<uint32_t>(kRsMaxFrames));
+        uint32_t *hs = reinterpret_cast<uint32_t *>(hist_state + static_cast<uint64_t>(sid) * 192);
+        const uint32_t *mw = reinterpret_cast<const uint32_t *>(pcm + m_in);
+        const uint32_t *hsrc = kind == GA_HIST_SLAB ? reinterpret_cast<const uint32_t *>(pcm + m_hist)
+                             : kind == GA_HIST_STATE ? hs : nullptr;
+        uint32_t v[2] = {0u, 0u};
+#pragma unroll
+        for (int t = 0; t < 2; t++) {
+            const int j = static_cast<int>(lane) + 32 * t;
+            // frame (nfr - 47 + j) of this message, or — for a short message — of the history before it
+            const int a = static_cast<int>(nfr) - kHist + j;
+            if (j < kHist) v[t] = a >= 0 ? mw[a] : (hsrc ? hsrc[kHist + a] : 0u);
+        }
+        __syncwarp();          // all reads of the old state are done before it is overwritten
+#pragma unroll
+        for (int t = 0; t < 2; t++) {
+            const int j = static_cast<int>(lane) + 32 * t;
+            if (j < kHist) hs[j] = v[t];
+        }
+        __syncwarp();
+    }
+}
+
 }  // namespace ga
 
 extern "C" int ga_k_resample48(const void *d_pcm, const ga_rdesc *d_desc, uint32_t n_msgs, void *d_hist_state,
@@ -416,5 +458,11 @@ extern "C" int ga_k_resample48(const void *d_pcm, const ga_rdesc *d_desc, uint32
     if (grid > want) grid = want;
     resample48_kernel<<<grid, kRsWarps * 32, smem, static_cast<cudaStream_t>(stream)>>>(p);
     GA_CHECK_LAUNCH("resample48_kernel");
+    if (d_hist_state) {
+        const uint32_t sgrid = ((n_msgs + 31) / 32 + kSaveWarps - 1) / kSaveWarps;
+        resample48_save_hist_kernel<<<sgrid, kSaveWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+            p.pcm, d_desc, p.hist_state, n_msgs);
+        GA_CHECK_LAUNCH("resample48_save_hist_kernel");
+    }
     return GA_OK;
 }

@@ -146,6 +146,37 @@ double ora_cpu_baseline(const uint8_t *pcm, uint32_t n_streams, uint32_t n_msgs,
                         uint32_t n_threads, int use_openssl,
                         uint8_t *digests_out, int32_t *winners_out, double *scores_out);
 
+/* The general form (ora_cpu_baseline above = mono, time-major, EVP).  See cpu_baseline.c for what
+ * each choice stands for in the Go path. */
+enum { ORA_FMT_MONO16K = 0, ORA_FMT_STEREO48K = 1 };         /* BASELINE configs[1,2,4] / configs[3] */
+enum { ORA_LAYOUT_TIME_MAJOR = 0, ORA_LAYOUT_STREAM_MAJOR = 1 };
+enum { ORA_SHA_PORT = 0, ORA_SHA_OPENSSL_EVP = 1, ORA_SHA_OPENSSL_LOW = 2 };
+typedef struct {
+    uint32_t n_streams, n_msgs, msg_bytes, wake_msgs, group_size;
+    uint32_t format;      /* ORA_FMT_*: 48 kHz stereo chunks go through the decimator (N2) instead of A1 */
+    uint32_t layout;      /* ORA_LAYOUT_*: chunk (s, m) at ((s*n_msgs + m) or (m*n_streams + s)) * msg_bytes */
+    uint32_t sha_impl;    /* ORA_SHA_* (falls back to the scalar port without OpenSSL)                   */
+    uint32_t n_threads;
+} ora_baseline_cfg;
+/* digests_out stays message-major [m][s][32] for either input layout. */
+double ora_cpu_baseline_run(const ora_baseline_cfg *cfg, const uint8_t *pcm, uint8_t *digests_out,
+                            int32_t *winners_out, double *scores_out);
+/* Plain memcpy bandwidth of n_threads host threads (GB/s, read + write): the ceiling a
+ * memory-bound baseline could not exceed, printed beside the thread-scaling table. */
+double ora_memcpy_gbs(uint32_t n_threads, size_t bytes_per_thread, uint32_t reps);
+
+/* ------------------------------------------------------------------ synthetic input */
+/* The integer-only synthetic relay PCM of SURVEY.md §8d, restated for the CPU arms (the GPU
+ * arm generates the same bytes on the device; tests compare the two).  Stream s is relay
+ * s % group_size of collision group group_base + s / group_size; n_msgs messages of msg_samples
+ * 16 kHz samples each.  stereo48 != 0: 3x zero-order hold to 48 kHz, R = L - (L >> 3), i.e.
+ * msg_samples*3 interleaved stereo frames (12 bytes per 16 kHz sample) per message.
+ * layout: ORA_LAYOUT_*.  n_threads workers. */
+void ora_synth_fill(void *out, uint64_t seed, uint32_t group_base, uint32_t n_streams,
+                    uint32_t group_size, uint32_t n_msgs, uint32_t msg_samples, int stereo48,
+                    uint32_t layout, uint32_t n_threads);
+int16_t ora_synth_sample(uint64_t seed, uint32_t group, uint32_t relay, uint32_t n, uint32_t utt_samples);
+
 #ifdef __cplusplus
 }
 #endif

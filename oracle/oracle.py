@@ -32,6 +32,16 @@ class ResampleState(C.Structure):
                 ("n_frames", C.c_uint64)]
 
 
+class BaselineCfg(C.Structure):
+    _fields_ = [(n, C.c_uint32) for n in ("n_streams", "n_msgs", "msg_bytes", "wake_msgs", "group_size",
+                                          "format", "layout", "sha_impl", "n_threads")]
+
+
+FMT_MONO16K, FMT_STEREO48K = 0, 1
+LAYOUT_TIME_MAJOR, LAYOUT_STREAM_MAJOR = 0, 1
+SHA_PORT, SHA_OPENSSL_EVP, SHA_OPENSSL_LOW = 0, 1, 2
+SYNTH_SEED = 0x10CA0B2000000001
+
 FRAME_DTYPE = np.dtype([("sumsq", "<f8"), ("rms", "<f8"), ("n_samples", "<u4"),
                         ("nonzero", "<u4"), ("peak", "<f4"), ("vad", "<u4")])
 
@@ -41,7 +51,7 @@ _lib = None
 def build(force=False):
     if force or not os.path.exists(_SO) or any(
             os.path.getmtime(os.path.join(_HERE, f)) > os.path.getmtime(_SO)
-            for f in ("gpuaudio_oracle.c", "cpu_baseline.c", "gpuaudio_oracle.h", "Makefile")):
+            for f in ("gpuaudio_oracle.c", "cpu_baseline.c", "synth_oracle.c", "gpuaudio_oracle.h", "Makefile")):
         subprocess.check_call(["make", "-C", _HERE, "-B"], stdout=subprocess.DEVNULL)
     return _SO
 
@@ -80,6 +90,15 @@ def lib():
         L.ora_cpu_baseline.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
                                        C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p,
                                        C.c_void_p]
+        L.ora_cpu_baseline_run.restype = C.c_double
+        L.ora_cpu_baseline_run.argtypes = [C.POINTER(BaselineCfg), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ora_memcpy_gbs.restype = C.c_double
+        L.ora_memcpy_gbs.argtypes = [C.c_uint32, C.c_size_t, C.c_uint32]
+        L.ora_synth_fill.restype = None
+        L.ora_synth_fill.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
+                                     C.c_uint32, C.c_int, C.c_uint32, C.c_uint32]
+        L.ora_synth_sample.restype = C.c_int16
+        L.ora_synth_sample.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
         _ = u8p
         _lib = L
     return _lib
@@ -210,3 +229,38 @@ def cpu_baseline(pcm, n_streams, n_msgs, msg_bytes, wake_msgs, group_size, n_thr
     t = lib().ora_cpu_baseline(_ptr(buf), n_streams, n_msgs, msg_bytes, wake_msgs, group_size,
                                n_threads, 1 if use_openssl else 0, _ptr(dg), _ptr(wn), _ptr(sc))
     return t, dg, wn, sc
+
+
+def cpu_baseline_run(pcm, n_streams, n_msgs, msg_bytes, wake_msgs, group_size, n_threads,
+                     fmt=FMT_MONO16K, layout=LAYOUT_STREAM_MAJOR, sha_impl=SHA_OPENSSL_LOW,
+                     want_outputs=False):
+    """General form of the timed CPU baseline (gpuaudio_oracle.h: ora_cpu_baseline_run).
+    Returns (seconds, digests [n_msgs][n_streams][32] | None, winners | None, scores | None)."""
+    buf = np.ascontiguousarray(pcm).view(np.uint8).reshape(-1)
+    assert buf.size >= n_streams * n_msgs * msg_bytes
+    cfg = BaselineCfg(n_streams, n_msgs, msg_bytes, wake_msgs, group_size, fmt, layout, sha_impl, n_threads)
+    dg = np.empty((n_msgs, n_streams, 32), dtype=np.uint8) if want_outputs else None
+    wn = np.empty(n_streams // max(group_size, 1), dtype=np.int32) if want_outputs else None
+    sc = np.empty(n_streams, dtype=np.float64) if want_outputs else None
+    t = lib().ora_cpu_baseline_run(C.byref(cfg), _ptr(buf), _ptr(dg), _ptr(wn), _ptr(sc))
+    return t, dg, wn, sc
+
+
+def memcpy_gbs(n_threads, bytes_per_thread=64 << 20, reps=8):
+    return lib().ora_memcpy_gbs(n_threads, bytes_per_thread, reps)
+
+
+def synth_fill(group_base, n_streams, group_size, n_msgs, msg_samples, stereo48=False,
+               layout=LAYOUT_STREAM_MAJOR, n_threads=1, seed=SYNTH_SEED):
+    """int16 array of the synthetic batch (gpuaudio_oracle.h: ora_synth_fill); shape
+    [n_streams][n_msgs][k] (stream-major) or [n_msgs][n_streams][k] (time-major), k = int16 per message."""
+    k = msg_samples * (6 if stereo48 else 1)
+    shape = (n_streams, n_msgs, k) if layout == LAYOUT_STREAM_MAJOR else (n_msgs, n_streams, k)
+    out = np.empty(shape, dtype=np.int16)
+    lib().ora_synth_fill(_ptr(out), seed, group_base, n_streams, group_size, n_msgs, msg_samples,
+                         1 if stereo48 else 0, layout, n_threads)
+    return out
+
+
+def synth_sample(group, relay, n, utt_samples, seed=SYNTH_SEED):
+    return int(lib().ora_synth_sample(seed, group, relay, n, utt_samples))

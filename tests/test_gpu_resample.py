@@ -118,6 +118,59 @@ def test_history_carries_across_batches_and_odd_chunk_sizes(ctx48):
         assert struct.pack("<d", res["rms"][i]) == struct.pack("<d", ora.signal_strength(y)[0])
 
 
+def test_saved_history_is_not_overwritten_while_an_earlier_chunk_still_needs_it(ctx48):
+    """A batch of more than 32 messages in which streams have their first chunk (history from the
+    state saved by the PREVIOUS batch, n0 != 0) in one 32-message group and their last chunk (which
+    saves the state for the NEXT batch) in another: the save must not reach the state before every
+    read of it is done.  Messages 31 / 32 of one stream is the tightest case (end of group 0, start
+    of group 1).  Repeated over three batches so the saved state is also consumed again."""
+    rng = np.random.default_rng(17)
+    n_streams, fr = 40, 960
+    per = {s: [] for s in range(n_streams)}
+    pcm = {s: np.stack([rng.integers(-30000, 30000, 12 * fr), rng.integers(-30000, 30000, 12 * fr)], axis=1).astype("<i2")
+           for s in range(n_streams)}
+    taken = {s: 0 for s in range(n_streams)}
+
+    def next_chunk(s, frames=fr):
+        c = pcm[s][taken[s]:taken[s] + frames].tobytes()
+        taken[s] += frames
+        per[s].append(c)
+        return c
+
+    got = {s: [] for s in range(n_streams)}
+
+    def run(order, first=False, frames=None):
+        chunks = [next_chunk(s, (frames or {}).get(i, fr)) for i, s in enumerate(order)]
+        seen = set()
+        fl = []
+        for s in order:
+            fl.append(L.MSG_FIRST if first and s not in seen else 0)
+            seen.add(s)
+        res, _ = ctx48.ingest(chunks, np.array(order, np.uint32), np.array(fl, np.uint32))
+        for i, s in enumerate(order):
+            got[s].append(res[i])
+
+    run(list(range(n_streams)), first=True, frames={i: 700 + 3 * i + (i % 3) for i in range(n_streams)})   # n0 != 0 afterwards
+    # batch 2: stream 7 sits at messages 31 and 32; 31 other streams fill the rest of group 0 and
+    # come back (their saving chunk) in groups 1-3
+    front = [s for s in range(32) if s != 7]
+    order = front + [7, 7] + front + list(range(32, 40)) + front[::2]
+    assert len(front) == 31 and order[31] == 7 and order[32] == 7 and 7 not in front and len(order) > 96
+    run(order)
+    # batch 3: every stream again, first chunks spread over two groups, second chunks behind them
+    run(list(range(n_streams)) + list(range(n_streams - 1, -1, -1)))
+    for s in range(n_streams):
+        parts = oracle_stream(per[s])
+        assert np.array_equal(bits(ctx48.fetch_samples(s)), bits(np.concatenate(parts))), s
+        for r, data, y in zip(got[s], per[s], parts):
+            assert r["digest"].tobytes() == ora.sha256(data)
+            rms, st = ora.signal_strength(y)
+            assert r["n_samples"] == y.size and r["nonzero"] == st.nonzero
+            assert struct.pack("<d", r["sumsq"]) == struct.pack("<d", st.sumsq)
+            assert struct.pack("<d", r["rms"]) == struct.pack("<d", rms)
+            assert bits(r["peak"]) == bits(st.peak)
+
+
 def test_48k_boundary_rules(ctx48):
     with pytest.raises(L.GpuAudioError) as e:
         ctx48.ingest([b"\x00" * 3844], [1], [L.MSG_FIRST])

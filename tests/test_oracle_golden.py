@@ -223,3 +223,50 @@ def test_committed_golden_fixture():
         assert struct.pack("<d", rms).hex() == case["rms_f64_hex"]
         assert struct.pack("<d", st2.sumsq).hex() == case["sumsq_f64_hex"]
         assert (st.nonzero, int(f32bits(st.peak))) == (case["nonzero"], case["peak_bits"])
+
+
+# ---------------------------------------------------------------- the timed CPU baseline and its input
+def test_oracle_synth_matches_the_numpy_statement_in_every_layout():
+    """oracle/synth_oracle.c (what `bench.py --impl reference` feeds the CPU arm with) against the
+    independent numpy statement of the same integer generator, mono and 48 kHz stereo."""
+    from loqa_hub_b200 import synth
+    S, gs, M, ms = 6, 3, 4, 320
+    sm = ora.synth_fill(5, S, gs, M, ms, layout=ora.LAYOUT_STREAM_MAJOR, n_threads=3)
+    tm = ora.synth_fill(5, S, gs, M, ms, layout=ora.LAYOUT_TIME_MAJOR, n_threads=2)
+    assert np.array_equal(tm, synth.batch_time_major(5, S, gs, M, ms))
+    assert np.array_equal(sm, tm.transpose(1, 0, 2))
+    assert ora.synth_sample(7, 2, 12345, 80000) == int(synth.relay_view(7, 2, 1, 80000, 12345)[0])
+    st = ora.synth_fill(5, S, gs, M, ms, stereo48=True, n_threads=2)
+    assert st.shape == (S, M, ms * 6)
+    left = np.repeat(sm.reshape(S, M * ms).astype(np.int32), 3, axis=1)
+    want = np.stack([left, left - (left >> 3)], axis=2).astype(np.int16).reshape(S, M, ms * 6)
+    assert np.array_equal(st, want)
+
+
+def test_cpu_baseline_outputs_do_not_depend_on_layout_threads_or_sha_implementation():
+    S, gs, M, ms, wake = 16, 4, 12, 320, 5
+    sm = ora.synth_fill(0, S, gs, M, ms, layout=ora.LAYOUT_STREAM_MAJOR)
+    tm = np.ascontiguousarray(sm.transpose(1, 0, 2))
+    _, dg0, wn0, sc0 = ora.cpu_baseline(tm.view(np.uint8).reshape(-1), S, M, ms * 2, wake, gs, 1,
+                                        use_openssl=False, want_outputs=True)
+    for impl in (ora.SHA_PORT, ora.SHA_OPENSSL_EVP, ora.SHA_OPENSSL_LOW):
+        for th in (1, 3):
+            _, dg, wn, sc = ora.cpu_baseline_run(sm, S, M, ms * 2, wake, gs, th, sha_impl=impl, want_outputs=True)
+            assert np.array_equal(dg, dg0) and np.array_equal(wn, wn0) and np.array_equal(sc, sc0)
+    assert dg0[3, 5].tobytes() == hashlib.sha256(sm[5, 3].tobytes()).digest()
+    assert list(wn0) == [0] * (S // gs)           # relay 0 has the highest gain in every group
+    assert sc0[5] == ora.signal_strength(ora.bytes_to_float32(sm[5, :wake].tobytes())[0])[0]
+
+
+def test_cpu_baseline_48k_leg_is_the_oracle_decimator_bit_for_bit():
+    """The 48 kHz leg of the timed baseline restates ora_resample_48k_stereo for speed (no malloc per
+    chunk, interleaved FMA chains); its scores must be those of the oracle functions."""
+    S, gs, M, ms, wake = 4, 2, 9, 320, 4
+    st = ora.synth_fill(3, S, gs, M, ms, stereo48=True)
+    _, dg, wn, sc = ora.cpu_baseline_run(st, S, M, ms * 12, wake, gs, 2, fmt=ora.FMT_STEREO48K, want_outputs=True)
+    for s in range(S):
+        r = ora.Resampler()
+        y = np.concatenate([r.process(st[s, m].tobytes()) for m in range(wake)])
+        assert struct.pack("<d", sc[s]) == struct.pack("<d", ora.signal_strength(y)[0])
+        assert dg[2, s].tobytes() == hashlib.sha256(st[s, 2].tobytes()).digest()
+    assert list(wn) == [0, 0]
