@@ -5,18 +5,23 @@
 
 One "step" is one pass of the hot path over one resident batch of synthetic relay PCM
 (SURVEY.md §8d "saturated mode"): every stream's whole 5 s utterance as 250 messages of
-20 ms, time-major as the chunks arrive.  Per GPU the default workload is BASELINE.json
-configs[2] (4,096 streams in 512 collision groups of 8 relays) — the smallest config that
-exercises all three parts of the metric; with N > 1 every rank holds one such shard and
-every 16th collision group spans two shards (configs[4]'s rule), so the scores of guest
-relays cross NVLink in one all-gather per step.  Weak scaling.
+20 ms, time-major as the chunks arrive.
+
+Workload by default:
+  N = 1   BASELINE.json configs[2] ("cfg3": 4,096 streams in 512 collision groups of 8 relays) — the
+          config the metric is quoted on; the JSON line also carries a short sweep of the other
+          single-GPU configs under "configs" (cfg2, cfg4 = 48 kHz stereo, cfg5_shard).
+  N > 1   BASELINE.json configs[4] ("cfg5": 65,536 streams sharded over the N GPUs by collision group,
+          every 16th group split over two shards so its window is arbitrated across NVLink).
 
 JSON keys (see DESIGN.md "Measurement"):
   value     audio-seconds / wall-second, device-resident inputs, CUDA events, max over ranks
-  e2e       same metric through the host C ABI (pinned ring -> ga_submit -> ga_wait ->
+  e2e       same metric through the host C ABI (pinned ring -> ga_submit_ticks -> ga_wait_view ->
             arbitration), H2D and D2H inside the timed region, host clock
-  roofline  the ingest kernel: algorithmic HBM bytes / its own CUDA-event time vs measured peak
-  cpu_baseline  oracle/ CPU restatement ("port": the Go reference cannot be built here)
+  roofline  the dominant kernel: what bounds it (integer ALU pipe for the SHA-256 instantiations, HBM
+            otherwise), live CUDA-event time per launch, algorithmic HBM bytes
+  cpu_baseline  oracle/ CPU restatement ("port": the Go reference cannot be built here) with its
+            thread-scaling table; `--impl reference` times the same thing as its own arm
 """
 import argparse
 import json
@@ -31,22 +36,39 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+TOTAL_CFG5_GROUPS = 8192      # configs[4]: 65,536 streams = 8,192 collision groups of 8 relays
 WORKLOADS = {
-    # name: (groups per GPU, relays per group, messages per stream, samples per message, wake msgs)
+    # groups: collision groups per GPU (cfg5: over all GPUs), relays per group, messages per stream,
+    # 16 kHz samples per message, wake-word messages
     "cfg2": dict(groups=1024, group_size=1, n_msgs=250, msg_samples=320, wake_msgs=15,
                  desc="configs[1]: 1,024 independent 16 kHz mono streams, 20 ms chunks"),
     "cfg3": dict(groups=512, group_size=8, n_msgs=250, msg_samples=320, wake_msgs=15,
                  desc="configs[2]: 4,096 streams in 512 collision groups of 8 relays, 20 ms chunks"),
     "cfg4": dict(groups=1024, group_size=8, n_msgs=250, msg_samples=320, wake_msgs=15, stereo48=True,
                  desc="configs[3]: 8,192 streams of 48 kHz stereo, 3,840 B chunks, resampled to 16 kHz mono"),
-    "cfg5": dict(groups=1024, group_size=8, n_msgs=250, msg_samples=320, wake_msgs=15,
-                 desc="configs[4] shard: 8,192 streams per GPU (65,536 over 8), cross-shard windows"),
+    "cfg5": dict(groups=TOTAL_CFG5_GROUPS, group_size=8, n_msgs=250, msg_samples=320, wake_msgs=15, strong=True,
+                 desc="configs[4]: 65,536 streams sharded by collision group, every 16th window spans two shards"),
+    "cfg5_shard": dict(groups=1024, group_size=8, n_msgs=250, msg_samples=320, wake_msgs=15,
+                       desc="configs[4], one of eight shards: 8,192 streams on one GPU"),
 }
-# dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
-# `ncu --set full` captures (profiles/r1_ncu_summary.md) at the default cfg3 size; None where no
-# capture exists for that variant.  Not measured live: a run under a profiler is never timed.
-NCU_TRAFFIC_BYTES = {("cfg3", "fused", "tmap"): 2_012_917_376, ("cfg3", "split", "tmap"): 2_006_581_592}
-NCU_ALU_PIPE_PCT = {("cfg3", "fused", "tmap"): 79.1}
+# Per-launch figures of the dominant kernel taken from committed `ncu` captures (never measured live:
+# a run under a profiler is not timed).  traffic = dram__bytes_read.sum + dram__bytes_write.sum;
+# alu_inst = sm__inst_executed_pipe_alu.sum (warp instructions); both scale with the message count,
+# so they are stored per message.  Source files under profiles/.
+NCU = {
+    # (kernel variant): bytes per message, ALU-pipe warp instructions per message, capture
+    "ingest_fused": dict(traffic_per_msg=2_012_917_376 / 1_024_000, alu_pct=79.1,
+                         capture="profiles/r1_ncu_summary.md (r1e)"),
+    "ingest_split_convert": dict(traffic_per_msg=2_006_581_592 / 1_024_000, alu_pct=None,
+                                 capture="profiles/r1_ncu_summary.md (r1f)"),
+    "ingest_sha_only": dict(traffic_per_msg=None, alu_pct=91.4, capture="profiles/r1_ncu_summary.md (r1f)"),
+    "resample48": dict(traffic_per_msg=13.06e9 / 2_048_000, alu_pct=None, capture="profiles/r1_ncu_resample_v4.md"),
+}
+NCU_OVERRIDE = os.path.join(ROOT, "profiles", "ncu_constants.json")    # refreshed by tools/ncu_summary.py
+if os.path.exists(NCU_OVERRIDE):
+    with open(NCU_OVERRIDE) as _f:
+        for _k, _v in json.load(_f).items():
+            NCU.setdefault(_k, {}).update(_v)
 # HBM bytes per audio-second with f32 samples materialised
 ALGO_BYTES_PER_AUDIO_S = 32_000 + 64_000 + 50 * 64
 ALGO_BYTES_PER_AUDIO_S_48K = 192_000 + 64_000 + 50 * 64
@@ -58,7 +80,8 @@ def parse():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS),
+                    help="default: cfg3 at --gpus 1, cfg5 at --gpus > 1")
     ap.add_argument("--mode", default="fused", choices=["fused", "split"],
                     help="fused: one ingest launch; split: convert+features launch, then SHA-256 launch")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
@@ -73,8 +96,14 @@ def parse():
                          "or ga_submit with one 32-byte descriptor per message")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-sweep", action="store_true", help="N = 1: skip the cfg2 / cfg4 / cfg5_shard sweep")
+    ap.add_argument("--sweep-steps", type=int, default=5)
+    ap.add_argument("--fill-threads", type=int, default=8, help="host threads of the e2e_with_fill leg")
     ap.add_argument("--cpu-threads", type=int, default=0)
-    return ap.parse_args()
+    args = ap.parse_args()
+    if args.workload is None:
+        args.workload = "cfg3" if args.gpus == 1 else "cfg5"
+    return args
 
 
 def measured_peaks():
@@ -83,6 +112,24 @@ def measured_peaks():
         with open(p) as f:
             return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
     return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def workload_config(name, world):
+    """The `config` object both arms print (identical, so the driver can tell they ran the same thing)."""
+    w = WORKLOADS[name]
+    groups = w["groups"] if w.get("strong") else w["groups"] * world
+    return {"workload": name + ": " + w["desc"] + "; 5 s utterances as 250 x 20 ms chunks, saturated mode",
+            "streams_total": groups * w["group_size"], "n_gpus": world,
+            "scaling": "strong" if w.get("strong") else "weak"}
+
+
+def groups_per_gpu(name, world):
+    w = WORKLOADS[name]
+    if w.get("strong"):
+        if w["groups"] % world:
+            raise SystemExit("bench: %s needs --gpus to divide %d" % (name, w["groups"]))
+        return w["groups"] // world
+    return w["groups"]
 
 
 class ClockSampler:
@@ -135,60 +182,6 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_threads(args):
-    return args.cpu_threads or len(os.sched_getaffinity(0))
-
-
-def run_cpu(pcm_u8, w, n_streams, threads, min_core_seconds, max_seconds):
-    """Timed CPU baseline over whole batches until enough CPU work has been done."""
-    from oracle import oracle as ora
-    audio_s_batch = n_streams * w["n_msgs"] * w["msg_samples"] / 16000.0
-    total_t, reps = 0.0, 0
-    while reps == 0 or (total_t * threads < min_core_seconds and total_t < max_seconds):
-        t, _, _, _ = ora.cpu_baseline(pcm_u8, n_streams, w["n_msgs"], w["msg_samples"] * 2,
-                                      w["wake_msgs"], w["group_size"], threads, use_openssl=True)
-        total_t += t
-        reps += 1
-    return audio_s_batch * reps / total_t, reps, total_t, ora.have_openssl()
-
-
-def reference_arm(args, w):
-    """--impl reference: the reference's CPU path (oracle port — no Go toolchain here) on all
-    host cores, same workload / metric / unit.  Rank 0 only; never touches the GPU."""
-    if int(os.environ.get("RANK", "0")) != 0:
-        return
-    from loqa_hub_b200 import api, synth
-    from oracle import oracle as ora
-    ora.build()
-    threads = cpu_threads(args)
-    n_streams = w["groups"] * w["group_size"]
-    pcm = api.synth_batch_host(synth.SEED, 0, n_streams, w["group_size"], w["n_msgs"],
-                               w["msg_samples"], n_threads=threads)
-    pcm_u8 = pcm.view(np.uint8)
-    audio_s = n_streams * w["n_msgs"] * w["msg_samples"] / 16000.0
-    times = []
-    for i in range(args.warmup + args.steps):
-        t, _, _, _ = ora.cpu_baseline(pcm_u8, n_streams, w["n_msgs"], w["msg_samples"] * 2,
-                                      w["wake_msgs"], w["group_size"], threads, use_openssl=True)
-        if i >= args.warmup:
-            times.append(t)
-    total = sum(times)
-    value = audio_s * len(times) / total
-    sample = "%d streams x %d msgs of %d B per step (the full %s batch), OpenSSL SHA-256=%s" % (
-        n_streams, w["n_msgs"], w["msg_samples"] * 2, args.workload, bool(ora.have_openssl()))
-    emit({
-        "impl": "reference", "metric": "audio_seconds_per_second", "value": value, "unit": "audio-s/s",
-        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": 1e3 * total / len(times), "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "u32/f32/f64", "data": "synthetic",
-        "config": {"workload": args.workload + ": " + w["desc"], "streams": n_streams,
-                   "note": "CPU only: one batch per step regardless of --gpus"},
-        "cpu_baseline": {"value": value, "unit": "audio-s/s", "cores": threads, "kind": "port",
-                         "sample": sample},
-        "e2e": {"value": value, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    })
-
-
 _JSON_FD = None
 
 
@@ -211,41 +204,187 @@ def emit(obj):
         os.write(_JSON_FD, line)
 
 
-def main():
-    args = parse()
-    claim_stdout()
-    w = WORKLOADS[args.workload]
-    if args.impl == "reference":
-        reference_arm(args, w)
-        return
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
 
-    import torch
-    import torch.distributed as dist
-    import __graft_entry__ as entry
+
+# ============================================================================ CPU arm (oracle/ only)
+def host_threads(args):
+    return args.cpu_threads or len(os.sched_getaffinity(0))
+
+
+def thread_ladder(n):
+    out, t = [], 1
+    while t < n:
+        out.append(t)
+        t *= 2
+    out.append(n)
+    return out
+
+
+class CpuArm:
+    """The reference's CPU path for one workload: oracle/cpu_baseline.c on a bounded, stream-major
+    sample of the workload generated by oracle/synth_oracle.c.  Nothing of the product is loaded."""
+
+    def __init__(self, name, threads):
+        from oracle import oracle as ora
+        ora.build()
+        self.ora, self.name, self.threads = ora, name, threads
+        w = WORKLOADS[name]
+        self.w = w
+        self.fmt48 = bool(w.get("stereo48"))
+        gs = w["group_size"]
+        # sample: at most 4,096 mono / 1,024 stereo streams, whole groups, at least 4 groups per thread
+        cap = 1024 if self.fmt48 else 4096
+        groups = max(1, min(w["groups"], cap // gs))
+        self.S = groups * gs
+        self.msg_bytes = w["msg_samples"] * (12 if self.fmt48 else 2)
+        self.pcm = ora.synth_fill(0, self.S, gs, w["n_msgs"], w["msg_samples"], stereo48=self.fmt48,
+                                  layout=ora.LAYOUT_STREAM_MAJOR, n_threads=threads)
+        self.sha = ora.SHA_OPENSSL_LOW if ora.have_openssl() else ora.SHA_PORT
+
+    def audio_s(self, n_streams):
+        return n_streams * self.w["n_msgs"] * self.w["msg_samples"] / 16000.0
+
+    def once(self, threads, n_streams=None):
+        n = n_streams or self.S
+        t, _, _, _ = self.ora.cpu_baseline_run(self.pcm, n, self.w["n_msgs"], self.msg_bytes, self.w["wake_msgs"],
+                                               self.w["group_size"], threads,
+                                               fmt=self.ora.FMT_STEREO48K if self.fmt48 else self.ora.FMT_MONO16K,
+                                               layout=self.ora.LAYOUT_STREAM_MAJOR, sha_impl=self.sha)
+        return t
+
+    def streams_for(self, threads):
+        """Fewer streams for few threads so that every ladder point costs about the same wall time."""
+        gs = self.w["group_size"]
+        n = self.S * threads // self.threads
+        n = max(gs * min(4 * threads, self.S // gs), n // gs * gs)
+        return min(self.S, n)
+
+    def scaling(self, seconds_per_point):
+        table = {}
+        for th in thread_ladder(self.threads):
+            n = self.streams_for(th)
+            self.once(th, n)                                   # warm: page in, spin the threads up
+            tot, reps = 0.0, 0
+            while reps == 0 or tot < seconds_per_point:
+                tot += self.once(th, n)
+                reps += 1
+            table[str(th)] = self.audio_s(n) * reps / tot
+        return table
+
+    def describe(self, table, best):
+        one = table.get("1")
+        allc = table[str(self.threads)]
+        memcpy = {str(t): round(self.ora.memcpy_gbs(t), 1) for t in sorted({1, self.threads})}
+        return {"unit": "audio-s/s", "kind": "port", "cores": int(best), "host_threads": self.threads,
+                "scaling": {k: round(v, 1) for k, v in table.items()},
+                "scaling_efficiency_all_threads": round(allc / (one * self.threads), 3) if one else None,
+                "value_single_thread": one, "host_memcpy_gbs": memcpy,
+                "sha256": {self.ora.SHA_OPENSSL_LOW: "OpenSSL SHA256_Init/Update/Final (SHA-NI where present)",
+                           self.ora.SHA_PORT: "scalar port"}[self.sha],
+                "input": "stream-major (each worker's chunks contiguous, as gRPC hands them over), "
+                         "per-thread heap, no per-chunk logging"}
+
+
+def cpu_baseline_block(name, threads, seconds_per_point):
+    arm = CpuArm(name, threads)
+    table = arm.scaling(seconds_per_point)
+    best = max(table, key=lambda k: table[k])
+    d = arm.describe(table, best)
+    d["value"] = table[best]
+    d["sample"] = "%d of the workload's streams x %d msgs x %d B per pass (fewer at low thread counts), " \
+                  ">= %.1f s per thread count" % (arm.S, arm.w["n_msgs"], arm.msg_bytes, seconds_per_point)
+    return d
+
+
+def reference_arm(args):
+    """--impl reference: the reference's CPU path (oracle port — no Go toolchain here) with all the
+    host threads it can use, same workload / metric / unit.  Rank 0 only; never touches the GPU and
+    never loads the product's library."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    threads = host_threads(args)
+    arm = CpuArm(args.workload, threads)
+    table = arm.scaling(1.0)
+    best = int(max(table, key=lambda k: table[k]))
+    times = []
+    for i in range(args.warmup + args.steps):
+        t = arm.once(best)
+        if i >= args.warmup:
+            times.append(t)
+    total = sum(times)
+    value = arm.audio_s(arm.S) * len(times) / total
+    cpu = arm.describe(table, best)
+    cpu["value"] = value
+    cpu["sample"] = "each step = %d of the workload's streams x %d msgs x %d B (whole 5 s utterances) on %d threads" % (
+        arm.S, arm.w["n_msgs"], arm.msg_bytes, best)
+    w = WORKLOADS[args.workload]
+    emit({
+        "impl": "reference", "metric": "audio_seconds_per_second", "value": value, "unit": "audio-s/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * total / len(times), "higher_is_better": True,
+        "scaling": "strong" if w.get("strong") else "weak",
+        "vs_baseline": None, "dtype": "u32/f32/f64", "data": "synthetic",
+        "config": workload_config(args.workload, args.gpus),
+        "cpu_baseline": cpu,
+        "e2e": {"value": value, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    })
+
+
+# ============================================================================ GPU arm
+class Env:
+    """Per-process state shared by the workloads of one run."""
+
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist, self.args = torch, dist, args
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        if self.world != args.gpus and self.world > 1:
+            raise SystemExit("--gpus %d but WORLD_SIZE=%d" % (args.gpus, self.world))
+        torch.cuda.set_device(self.local_rank)
+        self.dev = torch.device("cuda", self.local_rank)
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=self.dev)
+            dist.barrier()
+        self.stream = torch.cuda.current_stream()
+        self.sp = self.stream.cuda_stream
+
+    def sync_all(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier()
+            self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, x):
+        if self.world == 1:
+            return float(x)
+        t = self.torch.tensor([x], dtype=self.torch.float64, device=self.dev)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+
+def run_workload(env, name, steps, warmup, do_e2e):
+    """value / roofline / e2e of one workload on this process's GPU (all ranks call it together)."""
     from loqa_hub_b200 import _lib as L
     from loqa_hub_b200 import api, sharding, synth
+    torch, dist, args = env.torch, env.dist, env.args
+    rank, world, dev, stream, sp = env.rank, env.world, env.dev, env.stream, env.sp
+    w = WORKLOADS[name]
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != args.gpus and world > 1:
-        raise SystemExit("--gpus %d but WORLD_SIZE=%d" % (args.gpus, world))
-    if rank == 0:
-        entry.build()
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-        dist.barrier()
-    L.load()
-
-    plan = sharding.make_plan(rank, world, w["groups"], w["group_size"])
+    plan = sharding.make_plan(rank, world, groups_per_gpu(name, world), w["group_size"])
     S, M, ms, wake = plan.n_streams, w["n_msgs"], w["msg_samples"], w["wake_msgs"]
     arena = M * ms
     n_msgs = S * M
-    audio_s_step = S * M * ms / 16000.0                     # per GPU
-    stream = torch.cuda.current_stream()
-    sp = stream.cuda_stream
+    audio_s_step = S * M * ms / 16000.0                     # this GPU
+    audio_s_job = audio_s_step
+    if world > 1:
+        t = torch.tensor([audio_s_step], dtype=torch.float64, device=dev)
+        dist.all_reduce(t)                                  # shards differ by their guest streams
+        audio_s_job = float(t.item())
 
     def dptr(t):
         return t.data_ptr()
@@ -278,6 +417,8 @@ def main():
         rd["hist_off"] = prev
         d_rdesc = torch.from_numpy(rd.view(np.uint8)).to(dev)
         d_hist = torch.zeros(S * 192, dtype=torch.uint8, device=dev)
+        del rd, prev
+    del descs, k, s_idx
     samples = torch.empty(S * arena + 4, dtype=torch.float32, device=dev)
     results = torch.empty(n_msgs * 64, dtype=torch.uint8, device=dev)
 
@@ -298,7 +439,7 @@ def main():
     n_route = len(plan.route_dst)
 
     ingest_ev, resample_ev = [], []
-    exchange = None
+    exchange = region = None
     if world > 1 and args.exchange == "p2p":
         from loqa_hub_b200 import p2p
         region = p2p.Region(plan.n_guest_max, world)
@@ -336,7 +477,7 @@ def main():
         if timed:
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record(stream)
-        if fmt48:       # fingerprint of the received bytes (timed as the dominant kernel), then the decimator
+        if fmt48:       # fingerprint of the received bytes, then the decimator
             ingest(L.DO_SHA256, 0)
         elif args.mode == "fused":
             ingest(L.DO_ALL, dptr(samples))
@@ -357,134 +498,170 @@ def main():
             ingest(L.DO_SHA256, 0)
         arbitration(dptr(samples))
 
-    def sync_all():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-            torch.cuda.synchronize()
-
-    for _ in range(max(args.warmup, 3)):
+    for _ in range(max(warmup, 3)):
         step(False)
-    sync_all()
+    env.sync_all()
     launches0 = api.launch_count()
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local_rank) as clk:
-        sync_all()
+    with ClockSampler(env.local_rank) as clk:
+        env.sync_all()
         t0.record(stream)
-        for _ in range(args.steps):
+        for _ in range(steps):
             step(True)
         t1.record(stream)
-        sync_all()
+        env.sync_all()
     launches = api.launch_count() - launches0
-    elapsed_ms = t0.elapsed_time(t1)
     ingest_ms = float(np.mean([a.elapsed_time(b) for a, b in ingest_ev]))
-    if world > 1:
-        t = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        elapsed_ms = float(t.item())
-    value = audio_s_step * world * args.steps / (elapsed_ms * 1e-3)
+    elapsed_ms = env.max_over_ranks(t0.elapsed_time(t1))
+    value = audio_s_job * steps / (elapsed_ms * 1e-3)
 
-    # ---- correctness spot check of the resident run (cheap, outside the timed region)
+    # ---- correctness spot checks of the resident run (cheap, outside the timed region)
+    import hashlib
     win = d_winner.cpu().numpy().astype(np.int64)
     expect = plan.seg_offsets[:-1].astype(np.int64)      # relay 0 has the highest gain in every group
     if not np.array_equal(win, expect):
-        raise SystemExit("bench: arbitration winners are wrong on rank %d" % rank)
-    if fmt48:           # a digest of the resident run against hashlib (message 0 and the last one)
-        import hashlib
-        rec = results.view(torch.uint8).reshape(n_msgs, 64)
-        for mchk in (0, n_msgs - 1):
-            raw = pcm.view(torch.uint8)[mchk * msg_bytes:(mchk + 1) * msg_bytes].cpu().numpy().tobytes()
-            if rec[mchk, :32].cpu().numpy().tobytes() != hashlib.sha256(raw).digest():
-                raise SystemExit("bench: 48 kHz digest of message %d is wrong on rank %d" % (mchk, rank))
+        raise SystemExit("bench: arbitration winners are wrong on rank %d (%s)" % (rank, name))
+    rec = results.view(torch.uint8).reshape(n_msgs, 64)
+    for mchk in (0, n_msgs // 2 + 17, n_msgs - 1):        # digests against hashlib, not the oracle
+        raw = pcm.view(torch.uint8)[mchk * msg_bytes:(mchk + 1) * msg_bytes].cpu().numpy().tobytes()
+        if rec[mchk, :32].cpu().numpy().tobytes() != hashlib.sha256(raw).digest():
+            raise SystemExit("bench: digest of message %d is wrong on rank %d (%s)" % (mchk, rank, name))
+    if not fmt48:   # one stream's converted samples against IEEE float32 division in numpy (audio_service.go:1078)
+        s_chk = S // 3
+        raw = pcm.view(M, S, ms)[:, s_chk, :].cpu().numpy().reshape(-1)
+        want = raw.astype(np.float32) / np.float32(32767.0)
+        got = samples[s_chk * arena:(s_chk + 1) * arena].cpu().numpy()
+        if not np.array_equal(got.view(np.uint32), want.view(np.uint32)):
+            raise SystemExit("bench: converted samples of stream %d are wrong on rank %d (%s)" % (s_chk, rank, name))
     if exchange is not None and exchange.error_flag():
         raise SystemExit("bench: cross-shard exchange timed out on rank %d" % rank)
-    if world > 1:
+    if world > 1 and n_guest:
         # the scores that crossed shards must be the guests' true scores: compare the routed slots
         # with the same relays scored where they live (all-gathered once, outside the timed region)
         mine = d_scores[n_slots:].clone()
-        allg = torch.zeros(max(world * n_guest, 1), dtype=torch.float64, device=dev)
-        if n_guest:
-            dist.all_gather_into_tensor(allg, mine)
-            got = d_scores[:n_slots].cpu().numpy()[plan.route_dst]
-            if not np.array_equal(got, allg.cpu().numpy()[plan.route_src]):
-                raise SystemExit("bench: routed cross-shard scores are wrong on rank %d" % rank)
+        allg = torch.zeros(world * n_guest, dtype=torch.float64, device=dev)
+        dist.all_gather_into_tensor(allg, mine)
+        got = d_scores[:n_slots].cpu().numpy()[plan.route_dst]
+        if not np.array_equal(got, allg.cpu().numpy()[plan.route_src]):
+            raise SystemExit("bench: routed cross-shard scores are wrong on rank %d" % rank)
 
     # ---- end to end through the host C ABI
     e2e = None
-    if not args.no_e2e:
-        with ClockSampler(local_rank) as clk2:
-            e2e = run_e2e(args, w, plan, pcm, arbitration, d_winner, world, rank, local_rank, dev)
+    if do_e2e:
+        with ClockSampler(env.local_rank) as clk2:
+            e2e = run_e2e(env, w, plan, pcm, arbitration, d_winner, steps)
         clk.lines += clk2.lines
 
-    # ---- CPU baseline (rank 0, N = 1 only)
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline and not fmt48:
-        from oracle import oracle as ora
-        ora.build()
-        threads = cpu_threads(args)
-        host_pcm = pcm.cpu().numpy().view(np.uint8)
-        v, reps, tt, ssl = run_cpu(host_pcm, w, S, threads, min_core_seconds=20.0, max_seconds=20.0)
-        # one thread = one reference goroutine working alone (SURVEY.md §8d shape 1), on 1/8 of the streams
-        s1 = max(w["group_size"], S // 8 // w["group_size"] * w["group_size"])
-        pcm1 = np.ascontiguousarray(host_pcm.reshape(M, S, ms * 2)[:, :s1, :])
-        v1, _, _, _ = run_cpu(pcm1.reshape(-1), w, s1, 1, min_core_seconds=0.0, max_seconds=0.0)
-        cpu = {"value": v, "unit": "audio-s/s", "cores": threads, "kind": "port", "value_single_thread": v1,
-               "sample": "%d x the full batch (%d streams x %d msgs x %d B) in %.2f s, OpenSSL SHA-256=%s, "
-                         "no per-chunk logging" % (reps, S, M, ms * 2, tt, bool(ssl))}
+    # ---- roofline of the dominant kernel
+    peak, peak_src = measured_peaks()
+    algo_bytes = (ALGO_BYTES_PER_AUDIO_S_48K if fmt48 else ALGO_BYTES_PER_AUDIO_S) * audio_s_step
+    sha_runs = fmt48 or args.mode == "fused"
+    kern = "ingest_sha_only" if fmt48 else ("ingest_fused" if args.mode == "fused" else "ingest_split_convert")
+    ncu = NCU.get(kern, {})
+    clocks = clk.summary()
 
-    if world > 1:
-        dist.barrier()
-    if rank == 0:
-        peak, peak_src = measured_peaks()
-        algo_bytes = (ALGO_BYTES_PER_AUDIO_S_48K if fmt48 else ALGO_BYTES_PER_AUDIO_S) * audio_s_step
-        achieved = algo_bytes / (ingest_ms * 1e-3) / 1e9
-        out = {
-            "metric": "audio_seconds_per_second", "value": value, "unit": "audio-s/s", "n_gpus": world,
-            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": elapsed_ms / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32/f32/f64",
-            "data": "synthetic",
-            "config": {"workload": args.workload + " per GPU: " + w["desc"] + "; 5 s utterances, saturated mode",
-                       "streams_per_gpu": S, "msgs_per_step_per_gpu": n_msgs, "mode": args.mode,
-                       "staging": args.staging,
-                       "cross_shard_windows_per_gpu": plan.n_spanning_windows,
-                       "exchange": (args.exchange if world > 1 else "none"),
-                       "l2": "inputs %.0f MB + outputs %.0f MB per step > 126 MB L2, no flush needed" % (
-                           n_msgs * ms * 2 / 1e6, n_msgs * (ms * 4 + 64) / 1e6)},
-            "roofline": {"bound": "hbm", "kernel": "ingest_kernel<%s>" % ("sha256 of 48 kHz bytes" if fmt48 else args.mode), "achieved": achieved,
-                         "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": NCU_TRAFFIC_BYTES.get((args.workload, args.mode, args.staging)),
-                         "alu_pipe_pct_of_peak_ncu": NCU_ALU_PIPE_PCT.get((args.workload, args.mode, args.staging)),
-                         "peak_source": peak_src, "ms_per_launch": ingest_ms,
-                         "algorithmic_bytes_per_launch": algo_bytes,
-                         "note": "the fused kernel is bound by the integer ALU pipe (SHA-256), not by HBM: see "
-                                 "alu_pipe_pct_of_peak_ncu and profiles/r1_ncu_summary.md; traffic is per launch "
-                                 "from the committed ncu capture"},
-            "gpu_launches": int(launches),
-            "clocks": clk.summary(),
-        }
-        if fmt48:
-            rs_ms = float(np.mean([a.elapsed_time(b) for a, b in resample_ev]))
-            out["resample_kernel"] = {"ms_per_launch": rs_ms, "achieved_gbs": algo_bytes / (rs_ms * 1e-3) / 1e9,
-                                      "frac_of_hbm_peak": algo_bytes / (rs_ms * 1e-3) / 1e9 / peak,
-                                      "note": "resample48_kernel alone moves the 259,200 B per audio-s; the SHA-256 "
-                                              "launch reads the 192,000 B of PCM a second time"}
-        if cpu:
-            out["cpu_baseline"] = cpu
-        if e2e:
-            out["e2e"] = e2e
-        emit(out)
-    if world > 1:
-        dist.destroy_process_group()
+    def alu_block(ms_launch, key):
+        """Integer-ALU roofline of a SHA-256 instantiation: ALU-pipe warp instructions per launch (from
+        the committed ncu capture) / live time, against SMs x 4 schedulers x 0.5 warp instructions per
+        clock (a 16-lane pipe) at the SM clock sampled during the run."""
+        c = NCU.get(key, {})
+        per_msg = c.get("alu_inst_per_msg")
+        if per_msg is None:
+            return None
+        mhz = clocks.get("sm_mhz") or 1965.0
+        sms = torch.cuda.get_device_properties(dev).multi_processor_count
+        peak_ginst = sms * 4 * 0.5 * mhz * 1e-3
+        ach = per_msg * n_msgs / (ms_launch * 1e-3) / 1e9
+        return {"achieved": ach, "peak": peak_ginst, "unit": "G warp-inst/s", "frac": ach / peak_ginst,
+                "alu_inst_per_launch": per_msg * n_msgs, "sm_mhz": mhz, "capture": c.get("capture")}
+
+    hbm_ach = algo_bytes / (ingest_ms * 1e-3) / 1e9
+    roof = {"kernel": {"ingest_fused": "ingest_kernel<convert+features+sha256>",
+                       "ingest_split_convert": "ingest_kernel<convert+features>",
+                       "ingest_sha_only": "ingest_kernel<sha256 of the 48 kHz bytes>"}[kern],
+            "ms_per_launch": ingest_ms, "algorithmic_bytes_per_launch": algo_bytes,
+            "traffic": ncu["traffic_per_msg"] * n_msgs if ncu.get("traffic_per_msg") else None,
+            "traffic_source": ncu.get("capture"), "peak_source": peak_src}
+    alu = alu_block(ingest_ms, kern) if sha_runs else None
+    if sha_runs:
+        # bound by the integer ALU pipe (SHA-256), not by HBM
+        roof.update({"bound": "alu", "alu_pipe_pct_of_peak_ncu": ncu.get("alu_pct")})
+        if alu:
+            roof.update(alu)
+        else:       # no instruction count committed yet: the ncu percentage of the capture is the figure
+            roof.update({"achieved": ncu.get("alu_pct"), "peak": 100.0, "unit": "% of ALU-pipe peak (ncu capture)",
+                         "frac": (ncu.get("alu_pct") or 0.0) / 100.0})
+        roof.update({"hbm_achieved_gbs": hbm_ach, "hbm_peak_gbs": peak, "hbm_frac": hbm_ach / peak})
+        if fmt48:   # the fingerprint reads only the PCM: its own algorithmic bytes
+            sha_bytes = 192_000 * audio_s_step + 64.0 * n_msgs
+            roof.update({"algorithmic_bytes_per_launch": sha_bytes, "hbm_achieved_gbs": sha_bytes / (ingest_ms * 1e-3) / 1e9,
+                         "hbm_frac": sha_bytes / (ingest_ms * 1e-3) / 1e9 / peak})
+    else:
+        roof.update({"bound": "hbm", "achieved": hbm_ach, "peak": peak, "unit": "GB/s", "frac": hbm_ach / peak})
+
+    out = {
+        "metric": "audio_seconds_per_second", "value": value, "unit": "audio-s/s", "n_gpus": world,
+        "steps": steps, "warmup": max(warmup, 3), "ms_per_step": elapsed_ms / steps,
+        "higher_is_better": True, "scaling": "strong" if w.get("strong") else "weak", "vs_baseline": None,
+        "dtype": "u32/f32/f64", "data": "synthetic",
+        "config": workload_config(name, world),
+        "run": {"streams_this_gpu": S, "msgs_per_step_this_gpu": n_msgs, "mode": args.mode, "staging": args.staging,
+                "cross_shard_windows_this_gpu": plan.n_spanning_windows,
+                "exchange": (args.exchange if world > 1 else "none"),
+                "l2": "inputs %.0f MB + outputs %.0f MB per step > 126 MB L2, no flush needed" % (
+                    n_msgs * msg_bytes / 1e6, n_msgs * (ms * 4 + 64) / 1e6),
+                "checked": "winners, 3 digests vs hashlib, one stream's samples vs numpy IEEE division"
+                           + (", routed cross-shard scores" if world > 1 else "")},
+        "roofline": roof,
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+    }
+    if fmt48:
+        rs_ms = float(np.mean([a.elapsed_time(b) for a, b in resample_ev]))
+        rs_ach = algo_bytes / (rs_ms * 1e-3) / 1e9
+        c = NCU.get("resample48", {})
+        out["roofline_decimator"] = {
+            "kernel": "resample48_kernel (+ resample48_save_hist_kernel)", "bound": "hbm", "achieved": rs_ach, "peak": peak,
+            "unit": "GB/s", "frac": rs_ach / peak, "ms_per_launch": rs_ms, "algorithmic_bytes_per_launch": algo_bytes,
+            "traffic": c["traffic_per_msg"] * n_msgs if c.get("traffic_per_msg") else None,
+            "traffic_source": c.get("capture")}
+    if e2e:
+        out["e2e"] = e2e
+
+    env.sync_all()
+    return out          # the caller drops this frame's device tensors (gc + empty_cache) before the next workload
 
 
-def run_e2e(args, w, plan, pcm, arbitration, d_winner, world, rank, local_rank, dev):
+def h2d_ceiling(env, nbytes=256 << 20, reps=6):
+    """Bare pinned-host -> device copies, all ranks at once: what the platform gives the e2e leg."""
+    torch = env.torch
+    h = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+    d = torch.empty(nbytes, dtype=torch.uint8, device=env.dev)
+    d.copy_(h, non_blocking=True)
+    env.sync_all()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(env.stream)
+    for _ in range(reps):
+        d.copy_(h, non_blocking=True)
+    b.record(env.stream)
+    env.sync_all()
+    ms = env.max_over_ranks(a.elapsed_time(b))
+    return nbytes * reps / (ms * 1e-3) / 1e9
+
+
+def run_e2e(env, w, plan, pcm, arbitration, d_winner, steps):
     """The call sequence the Go shim makes: chunks already sit in the C-owned pinned ring;
-    every `ticks_per_submit` ticks one ga_submit (H2D + fused ingest + D2H of result records),
-    up to 4 tickets in flight; then arbitration and a D2H read of the winners."""
-    import torch
-    import torch.distributed as dist
+    every `ticks_per_submit` ticks one ga_submit_ticks (H2D + fused ingest + D2H of result records),
+    up to 4 tickets in flight; then arbitration and a D2H read of the winners.  A second timed pass
+    (`with_fill`) also copies the step's bytes from ordinary host memory into the ring with
+    --fill-threads threads inside the timed region — the work the relays' goroutines do."""
+    import ctypes as C
+    import hashlib
+    from concurrent.futures import ThreadPoolExecutor
     from loqa_hub_b200 import _lib as L
     from loqa_hub_b200 import api
+    torch, args = env.torch, env.args
+    world, rank = env.world, env.rank
 
     S, M, ms, wake = plan.n_streams, w["n_msgs"], w["msg_samples"], w["wake_msgs"]
     tps = max(1, min(args.ticks_per_submit, M))
@@ -494,19 +671,18 @@ def run_e2e(args, w, plan, pcm, arbitration, d_winner, world, rank, local_rank, 
     fmt48 = bool(w.get("stereo48"))
     chunk = ms * 12 if fmt48 else ms * 2
     sub_bytes = sub_msgs * chunk
-    # mono: the ring holds the whole step.  48 kHz stereo (7.9 GB per step): a ring of 5 submits that the
-    # step goes round five times — submits 5.. re-send the bytes of submits 0..4 (the wake-word part
-    # that arbitration reads is in submits 0-1 and is the real data)
-    n_host = n_sub if not fmt48 else min(n_sub, 5)
-    while n_sub % n_host:
+    # The ring holds the whole step when that is at most ~1.4 GB; otherwise it holds n_host submits and
+    # the step goes round it several times — later submits re-send the bytes of the first n_host (the
+    # wake-word part that arbitration reads is in submits 0-1 and is the real data)
+    n_host = n_sub
+    while n_host > 2 and (sub_bytes * n_host > (1400 << 20) or n_sub % n_host):
         n_host -= 1
     ring_bytes = sub_bytes * n_host
-    ctx = api.Context(device=local_rank, max_streams=S, max_batch_msgs=sub_msgs, max_inflight=4,
+    ctx = api.Context(device=env.local_rank, max_streams=S, max_batch_msgs=sub_msgs, max_inflight=4,
                       ring_bytes=ring_bytes, arena_samples=M * ms, wake_samples_max=wake * ms,
                       mode=L.DO_ALL, want_frames=False,
                       input_format=L.FMT_STEREO48K if fmt48 else L.FMT_MONO16K,
                       staging=L.STAGING_AUTO if args.staging == "tmap" else L.STAGING_BULK)
-    import ctypes as C
     arena_ptr = C.c_void_p()
     L.check(L.load().ga_device_arena(ctx._h, C.byref(arena_ptr)))
     host_pcm = pcm[: ring_bytes // 2].cpu().numpy().view(np.uint8)
@@ -532,13 +708,19 @@ def run_e2e(args, w, plan, pcm, arbitration, d_winner, world, rank, local_rank, 
     # per-message descriptors (32 B each, 96 B for 48 kHz) or, for ga_submit_ticks, 1 flag byte per message + 20 B per stream
     h2d = sub_bytes * n_sub + (n_sub * (sub_msgs + 20 * S) if ticks else sub_msgs * n_sub * (96 if fmt48 else 32))
     d2h = sub_msgs * n_sub * 64 + plan.n_windows * 4
+    nfill = max(1, args.fill_threads)
+    pool = ThreadPoolExecutor(nfill)
+    cuts = [sub_bytes * i // nfill // 64 * 64 for i in range(nfill)] + [sub_bytes]
+
+    def fill_block(view, src):          # numpy releases the GIL for large copies: nfill memcpys in parallel
+        list(pool.map(lambda i: np.copyto(view[cuts[i]:cuts[i + 1]], src[cuts[i]:cuts[i + 1]]), range(nfill)))
 
     def one_step(fill):
         tickets = []
         for j in range(n_sub):
             view, off = ctx.reserve(sub_bytes)
-            if fill:                                    # first pass only: the relays' bytes land in the ring
-                view[:sub_bytes] = host_pcm[(j % n_host) * sub_bytes:(j % n_host + 1) * sub_bytes]
+            if fill:                                    # the relays' bytes land in the ring
+                fill_block(view, host_pcm[(j % n_host) * sub_bytes:(j % n_host + 1) * sub_bytes])
             t = C.c_uint64()
             if ticks:
                 L.check(lib.ga_submit_ticks(ctx._h, off, tps, S, chunk, L.ptr(ids), L.ptr(tick_flags[j]), C.byref(t)))
@@ -554,41 +736,104 @@ def run_e2e(args, w, plan, pcm, arbitration, d_winner, world, rank, local_rank, 
         arbitration(arena_ptr.value)
         return d_winner.cpu()                           # D2H read of the step's result
 
-    def sync_all():
+    def check(win):
+        if not np.array_equal(win.numpy().astype(np.int64), plan.seg_offsets[:-1].astype(np.int64)):
+            raise SystemExit("bench: e2e arbitration winners are wrong on rank %d" % rank)
+        # one digest of the last sub-batch against hashlib (not the oracle)
+        jl = (n_sub - 1) % n_host
+        last = host_pcm[jl * sub_bytes:jl * sub_bytes + chunk].tobytes()
+        res_last = np.ctypeslib.as_array(C.cast(res_p, C.POINTER(C.c_uint8)), shape=(64,))
+        if res_last[:32].tobytes() != hashlib.sha256(last).digest():
+            raise SystemExit("bench: e2e digest mismatch on rank %d" % rank)
+
+    def timed(fill, steps):
+        env.sync_all()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            win = one_step(fill)
         torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
+        dt = env.max_over_ranks(time.perf_counter() - t0)
+        check(win)
+        return dt
 
     one_step(True)
     for _ in range(2):
         one_step(False)
-    sync_all()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        win = one_step(False)
-    torch.cuda.synchronize()
-    dt = time.perf_counter() - t0
-    if world > 1:
-        t = torch.tensor([dt], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dt = float(t.item())
-    if not np.array_equal(win.numpy().astype(np.int64), plan.seg_offsets[:-1].astype(np.int64)):
-        raise SystemExit("bench: e2e arbitration winners are wrong on rank %d" % rank)
-    # spot check one digest of the last sub-batch against hashlib (not the oracle)
-    import hashlib
-    jl = (n_sub - 1) % n_host
-    last = host_pcm[jl * sub_bytes:jl * sub_bytes + chunk].tobytes()
-    res_last = np.ctypeslib.as_array(C.cast(res_p, C.POINTER(C.c_uint8)), shape=(64,))
-    if res_last[:32].tobytes() != hashlib.sha256(last).digest():
-        raise SystemExit("bench: e2e digest mismatch on rank %d" % rank)
+    dt = timed(False, steps)
+    fill_steps = max(2, min(steps, 5))
+    dt_fill = timed(True, fill_steps)
     ctx.close()
-    audio_s = S * M * ms / 16000.0 * world
-    return {"value": audio_s * args.steps / dt, "unit": "audio-s/s", "h2d_bytes_per_step": int(h2d),
-            "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * dt / args.steps,
-            "h2d_gbs_per_gpu": h2d * args.steps / dt / 1e9,
-            "submit": "ga_submit_ticks" if ticks else "ga_submit",
-            "note": "host clock around %s/ga_wait/arbitration, %d submits of %d msgs per step, "
-                    "4 tickets in flight" % ("ga_submit_ticks" if ticks else "ga_submit", n_sub, sub_msgs)}
+    pool.shutdown()
+    ceiling = h2d_ceiling(env)
+    audio_s = S * M * ms / 16000.0
+    if world > 1:
+        t = torch.tensor([audio_s], dtype=torch.float64, device=env.dev)
+        env.dist.all_reduce(t)
+        audio_s = float(t.item())
+    name = "ga_submit_ticks" if ticks else "ga_submit"
+    return {"value": audio_s * steps / dt, "unit": "audio-s/s", "h2d_bytes_per_step": int(h2d),
+            "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * dt / steps,
+            "h2d_gbs_per_gpu": h2d * steps / dt / 1e9,
+            "h2d_ceiling_gbs_per_gpu": ceiling,
+            "submit": name,
+            "with_fill": {"value": audio_s * fill_steps / dt_fill, "ms_per_step": 1e3 * dt_fill / fill_steps,
+                          "steps": fill_steps, "fill_threads": nfill,
+                          "note": "as e2e, plus every step's bytes copied from ordinary host memory into the pinned "
+                                  "ring (ga_ring_reserve + memcpy) inside the timed region"},
+            "note": "host clock around %s/ga_wait_view/arbitration/D2H of winners; chunks already in the pinned ring "
+                    "(a relay's goroutine copies them there as they arrive; see with_fill); %d submits of %d msgs "
+                    "per step, 4 tickets in flight; h2d_ceiling = bare concurrent pinned copies in this run" % (
+                        name, n_sub, sub_msgs)}
+
+
+def main():
+    args = parse()
+    claim_stdout()
+    if args.impl == "reference":
+        reference_arm(args)
+        return
+
+    import gc
+    import __graft_entry__ as entry
+    rank = int(os.environ.get("RANK", "0"))
+    if rank == 0:
+        entry.build()
+    env = Env(args)
+    from loqa_hub_b200 import _lib as L
+    L.load()
+    torch = env.torch
+
+    out = run_workload(env, args.workload, args.steps, args.warmup, not args.no_e2e)
+    gc.collect()
+    torch.cuda.empty_cache()
+
+    if env.world == 1:
+        threads = host_threads(args)
+        if not args.no_cpu_baseline:
+            out["cpu_baseline"] = cpu_baseline_block(args.workload, threads, 2.0)
+        if not args.no_sweep:
+            # the other single-GPU configs, a few steps each, so their numbers are measured in the same run
+            sweep = {}
+            for name in ("cfg2", "cfg4", "cfg5_shard"):
+                if name == args.workload:
+                    continue
+                t0 = time.time()
+                r = run_workload(env, name, args.sweep_steps, 3, not args.no_e2e)
+                gc.collect()
+                torch.cuda.empty_cache()
+                keep = {k: r[k] for k in ("value", "unit", "steps", "ms_per_step", "config", "run", "roofline",
+                                          "roofline_decimator", "e2e", "gpu_launches") if k in r}
+                if not args.no_cpu_baseline and name in ("cfg2", "cfg4"):
+                    keep["cpu_baseline"] = cpu_baseline_block(name, threads, 1.0)
+                sweep[name] = keep
+                log("bench: sweep %s done in %.1f s" % (name, time.time() - t0))
+            out["configs"] = sweep
+    if env.world > 1:
+        env.dist.barrier()
+    if env.rank == 0:
+        emit(out)
+    if env.world > 1:
+        env.dist.destroy_process_group()
 
 
 if __name__ == "__main__":

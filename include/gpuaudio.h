@@ -224,8 +224,9 @@ int ga_k_resample48(const void *d_pcm, const ga_rdesc *d_desc, uint32_t n_msgs, 
  *
  * Inputs, rules and outputs are those of ga_k_arbitrate, minus the score array: the caller gets
  * winner[] and status_out[] only.  The per-member float64 scores, which sit between the scoring
- * launch and the selection launch, live in a 512 KiB array built into the library image; every
- * GPU the library is loaded on holds one copy until the process exits.  Consequences:
+ * launch and the selection launch, live in a 512 KiB array built into the library's device image;
+ * every GPU on which the CUDA runtime has loaded that image holds one copy until the process
+ * exits.  Consequences:
  *   - n_members may be at most 65,536 per call; more is refused with GA_ERR_OVERFLOW (split the
  *     windows over several calls, or use ga_k_arbitrate with a score array of your own);
  *   - the call makes no cudaMalloc / cudaFree and uses no allocating library routine;
@@ -234,7 +235,12 @@ int ga_k_resample48(const void *d_pcm, const ga_rdesc *d_desc, uint32_t n_msgs, 
  *     or different threads without ordering) race on it — serialise them on one stream or with
  *     events;
  *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress,
- *     with that device current); make that first call before any stream capture begins. */
+ *     with that device current).  With CUDA's default lazy module loading that lookup can be the
+ *     moment the driver places the library's image — this array included — on the device, which
+ *     allocates and synchronises once.  So make one warm-up call per device at start-up, with
+ *     that device current: before the host hands its HBM to its own pool and before any stream
+ *     capture begins.  A call with n_windows == 0 does exactly the set-up and nothing else (all
+ *     pointers may be NULL).  Later calls on that device only launch. */
 int ga_k_arbitrate_noalloc(const float *d_samples, const uint64_t *d_wake_off, const uint32_t *d_wake_n,
                            const uint8_t *d_status_in, const uint32_t *d_seg_offsets, uint32_t n_windows,
                            uint32_t n_members, uint32_t *d_winner, uint8_t *d_status_out, void *stream);
@@ -374,8 +380,11 @@ int ga_submit_ticks(ga_ctx *ctx, uint64_t ring_offset, uint32_t n_ticks, uint32_
 int ga_wait(ga_ctx *ctx, uint64_t ticket, ga_result *results, ga_frame *frames);
 int ga_ticket_frames(ga_ctx *ctx, uint64_t ticket, uint32_t *n_frames);
 /* Same as ga_wait without the copy: returns pointers into the C-owned pinned result buffers of
- * the ticket's slot (cgo wraps them with unsafe.Slice).  They stay valid until max_inflight
- * further ga_submit calls have been made.  Any out pointer may be NULL. */
+ * the ticket's slot (cgo wraps them with unsafe.Slice).  Slots are used round-robin, so the
+ * records of ticket t stay untouched until the ga_submit / ga_submit_ticks call that returns
+ * ticket t + max_inflight.  With max_inflight tickets outstanding when t is waited, that is the
+ * very next submit: read (or copy) the records before submitting again, or keep at most
+ * max_inflight - 1 tickets in flight.  Any out pointer may be NULL. */
 int ga_wait_view(ga_ctx *ctx, uint64_t ticket, const ga_result **results, const ga_frame **frames,
                  uint32_t *n_results, uint32_t *n_frames);
 
@@ -420,7 +429,8 @@ int ga_fetch_wav(ga_ctx *ctx, uint32_t stream_id, uint32_t sample_rate, uint8_t 
  * relay registry, arbitration-window lifecycle, per-chunk routing.  It is the logic the Go code
  * around this library keeps, provided in C++ so it can run and be tested
  * without a Go toolchain, and generalised from the reference's single hub-wide window (:89) to one
- * window per collision group.  Time is injected in microseconds.  Thread-safe (one mutex). */
+ * window per collision group.  Time is injected in microseconds.  Thread-safe: one mutex for the
+ * registry and the windows; the per-chunk path of speech chunks does not take it. */
 typedef struct ga_hub ga_hub;
 /* createAudioService :201-290; window_duration_us 0 = the reference's 300 ms (:243). */
 int  ga_hub_create(ga_ctx *ctx, uint32_t max_streams, uint64_t window_duration_us, ga_hub **out);
@@ -438,8 +448,23 @@ int  ga_hub_join_window(ga_hub *hub, const char *relay_id, uint64_t now_us, int 
  * end of speech :1018-1021). */
 int  ga_hub_on_chunk(ga_hub *hub, const char *relay_id, const uint8_t *audio, uint32_t nbytes,
                      int is_wake_word, int is_end_of_speech, uint64_t now_us, int *keep_stream);
-/* Batch tick: one ga_submit + wait for everything queued since the last flush (one more per
- * relay that restarted an utterance inside the tick; *n_msgs = messages taken off the queue). */
+/* The same through a handle, for the per-chunk path of a hub with thousands of relays: the handle
+ * (ga_hub_relay_handle, valid until the relay is cleaned up) stands for the relay's registry
+ * entry, so no name lookup and — for speech chunks, all but the first ~15 of an utterance — no
+ * hub-wide lock is taken: the reference's per-chunk streamsMutex (:1000-1004) is gone.  The bytes
+ * are copied into the pinned ring outside any lock.  Callable from many threads at once; one
+ * relay's chunks must come from one thread at a time, in order (its StreamAudio goroutine).
+ * GA_ERR_RING_FULL: the ring or the chunk queue is full until the next ga_hub_flush. */
+int  ga_hub_relay_handle(ga_hub *hub, const char *relay_id, uint64_t *handle);
+int  ga_hub_on_chunk_h(ga_hub *hub, uint64_t handle, const uint8_t *audio, uint32_t nbytes,
+                       int is_wake_word, int is_end_of_speech, uint64_t now_us, int *keep_stream);
+/* Batch tick: ga_submit + wait for everything queued since the last flush — one batch per GPU,
+ * more where a relay restarted an utterance inside the tick or the queue exceeds the context's
+ * max_batch_msgs (*n_msgs = messages ingested).  A relay whose sample arena is full (the
+ * reference appends without bound, :965 / :1002) loses its chunks of this tick and is taken out of
+ * activeStreams; everybody else's chunks are ingested and the call returns GA_ERR_OVERFLOW.  On any
+ * other failure the chunks not yet submitted stay queued for the next flush.  One flush at a time
+ * (calls serialise); chunks keep arriving meanwhile. */
 int  ga_hub_flush(ga_hub *hub, uint32_t *n_msgs);
 /* performArbitration :505-587 for one window (idempotent, :508-511) … */
 int  ga_hub_perform_arbitration(ga_hub *hub, uint64_t window_id);

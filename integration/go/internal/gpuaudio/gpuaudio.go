@@ -85,7 +85,9 @@ func (x *Ctx) SubmitTicks(off uint64, ticks int, slots []uint32, chunkBytes int,
 	return uint64(t), nil
 }
 
-// Wait returns a view of the C-owned pinned result records (valid for 4 more Submits).
+// Wait returns a view of the C-owned pinned result records.  Ticket t's records are overwritten by the
+// Submit that returns ticket t+4 (max_inflight): fan the results out before submitting again, or keep
+// at most 3 tickets in flight.
 func (x *Ctx) Wait(ticket uint64) ([]Result, error) {
 	var r *C.ga_result
 	var n C.uint32_t

@@ -206,8 +206,8 @@ class Context:
         return res, frames
 
     def wait_view(self, ticket):
-        """Zero-copy wait: numpy views of the pinned result buffers (valid until max_inflight
-        further submits)."""
+        """Zero-copy wait: numpy views of the pinned result buffers (ticket t's records are
+        overwritten by the submit that returns ticket t + max_inflight)."""
         self._pending.pop(ticket)
         pr, pf, nr, nf = C.c_void_p(), C.c_void_p(), C.c_uint32(), C.c_uint32()
         check(load().ga_wait_view(self._h, ticket, C.byref(pr), C.byref(pf), C.byref(nr), C.byref(nf)))

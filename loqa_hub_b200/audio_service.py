@@ -82,6 +82,19 @@ class AudioService:
                                          int(is_end_of_speech), now_us, C.byref(keep)))
         return bool(keep.value)
 
+    def relay_handle(self, relay_id):
+        hd = C.c_uint64()
+        L.check(L.load().ga_hub_relay_handle(self._h, relay_id.encode(), C.byref(hd)))
+        return hd.value
+
+    def on_chunk_h(self, handle, audio, is_wake_word, is_end_of_speech, now_us):
+        """ga_hub_on_chunk_h: the per-chunk path by handle (no name lookup, no hub lock for speech)."""
+        b = audio if isinstance(audio, np.ndarray) else np.frombuffer(bytes(audio), dtype=np.uint8)
+        keep = C.c_int()
+        L.check(L.load().ga_hub_on_chunk_h(self._h, handle, L.ptr(b), b.size, int(is_wake_word),
+                                           int(is_end_of_speech), now_us, C.byref(keep)))
+        return bool(keep.value)
+
     def flush(self):
         n = C.c_uint32()
         L.check(L.load().ga_hub_flush(self._h, C.byref(n)))

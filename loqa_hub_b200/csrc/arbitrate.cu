@@ -393,8 +393,10 @@ extern "C" int ga_k_arbitrate(const float *d_samples, const uint64_t *d_wake_off
 
 // ---------------------------------------------------------------- arbitration without allocation
 // Scratch for ga_k_arbitrate_noalloc: the per-member float64 scores that sit between the
-// scoring launch and the selection launch.  One copy lives in every GPU's memory from the
-// moment the library is loaded on it until the process exits (512 KiB).
+// scoring launch and the selection launch (512 KiB).  It is part of the library's device image:
+// every GPU on which the CUDA runtime has loaded that image holds one copy until the process
+// exits.  With CUDA's default lazy module loading that happens at the first use of the library
+// on a device, which can be this entry point's own first call there — the set-up below.
 #define GA_NOALLOC_MAX_MEMBERS 65536u
 static __device__ __align__(256) double g_noalloc_scores[GA_NOALLOC_MAX_MEMBERS];
 
@@ -414,6 +416,26 @@ extern "C" int ga_k_arbitrate_noalloc(const float *d_samples, const uint64_t *d_
                                       uint32_t *d_winner, uint8_t *d_status_out, void *stream)
 {
     using namespace ga;
+    int dev = 0;
+    GA_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) { set_error("ga_k_arbitrate_noalloc: device ordinal %d not supported", dev); return GA_ERR_ARG; }
+    double *scores = nullptr;
+    {
+        // Set-up, once per device, with that device current: the name g_noalloc_scores is only a
+        // host-side handle, a kernel needs the address the symbol has on THIS device.  Done before
+        // anything else so that a call with n_windows == 0 is a pure warm-up: under lazy module
+        // loading this lookup is where the driver may place the library's image (this array
+        // included) on the device, which allocates and synchronises — the one thing a caller that
+        // cannot allocate has to get out of the way at start-up.
+        std::lock_guard<std::mutex> lk(g_noalloc_mu);
+        if (!g_noalloc_ready[dev]) {
+            double *p = nullptr;
+            GA_CUDA_TRY(cudaGetSymbolAddress(reinterpret_cast<void **>(&p), g_noalloc_scores));
+            g_noalloc_ptr[dev] = p;
+            g_noalloc_ready[dev] = true;
+        }
+        scores = g_noalloc_ptr[dev];
+    }
     if (n_windows == 0) return GA_OK;
     if (!d_seg_offsets || !d_winner) { set_error("ga_k_arbitrate_noalloc: NULL argument"); return GA_ERR_ARG; }
     if (n_members && (!d_samples || !d_wake_off || !d_wake_n || !d_status_in || !d_status_out)) {
@@ -429,22 +451,6 @@ extern "C" int ga_k_arbitrate_noalloc(const float *d_samples, const uint64_t *d_
     if (reinterpret_cast<uintptr_t>(d_samples) & 15u) {
         set_error("ga_k_arbitrate_noalloc: d_samples must be 16-byte aligned");
         return GA_ERR_ARG;
-    }
-    int dev = 0;
-    GA_CUDA_TRY(cudaGetDevice(&dev));
-    if (dev < 0 || dev >= kMaxDevices) { set_error("ga_k_arbitrate_noalloc: device ordinal %d not supported", dev); return GA_ERR_ARG; }
-    double *scores = nullptr;
-    {
-        // Set-up, once per device, with that device current: the name g_noalloc_scores is only a
-        // host-side handle, a kernel needs the address the symbol has on THIS device.
-        std::lock_guard<std::mutex> lk(g_noalloc_mu);
-        if (!g_noalloc_ready[dev]) {
-            double *p = nullptr;
-            GA_CUDA_TRY(cudaGetSymbolAddress(reinterpret_cast<void **>(&p), g_noalloc_scores));
-            g_noalloc_ptr[dev] = p;
-            g_noalloc_ready[dev] = true;
-        }
-        scores = g_noalloc_ptr[dev];
     }
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     // The array still holds the previous call's scores: start this call's slots at 0.0 so a member

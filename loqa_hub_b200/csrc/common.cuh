@@ -51,6 +51,13 @@ extern std::atomic<uint64_t> g_launches;
 
 int num_sms(int *out);   // cached per current device
 
+// Library-internal entry points of the context layer used by the hub (csrc/hub.cu).
+// ga_submit with the index of the message a refusal is about (UINT32_MAX: not about one message).
+int submit_impl(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *ticket, uint32_t *bad_index);
+void ctx_limits(const ga_ctx *ctx, uint32_t *max_batch_msgs, uint64_t *frames_cap);
+// With no ticket in flight: the ring is free up to `off` (reservations that were dropped, not submitted).
+void ring_release_to(ga_ctx *ctx, uint64_t off);
+
 // ---------------------------------------------------------------- PTX: mbarrier + bulk copy
 // Shared-memory staging of message bytes uses the TMA engine's 1-D bulk copy
 // (cp.async.bulk -> SASS UBLKCP) completing on an mbarrier; one barrier per pipeline

@@ -14,6 +14,7 @@
 #include <mutex>
 #include <new>
 #include <thread>
+#include <utility>
 #include <vector>
 
 #include "common.cuh"
@@ -81,6 +82,7 @@ struct ga_ctx {
     std::vector<uint64_t> batch_stamp;         // 48 kHz input: ticket that last touched a stream ...
     std::vector<uint32_t> batch_last;          // ... and the index of that stream's latest message in it
     std::vector<uint64_t> tick_stamp;          // ga_submit_ticks: duplicate-stream check
+    std::vector<std::pair<uint32_t, uint64_t>> touched;   // ga_submit: (stream, stamp before this batch), for undo
     uint64_t frames_cap = 0;
     std::atomic<uint64_t> ring_head{0}, ring_tail{0};
     std::vector<ga::StreamState> streams;
@@ -325,15 +327,37 @@ static int fence_wait(ga_ctx *ctx, cudaStream_t s, uint64_t fence)
 
 extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *ticket)
 {
+    return ga::submit_impl(ctx, msgs, n, ticket, nullptr);
+}
+
+void ga::ctx_limits(const ga_ctx *ctx, uint32_t *max_batch_msgs, uint64_t *frames_cap)
+{
+    if (max_batch_msgs) *max_batch_msgs = ctx->cfg.max_batch_msgs;
+    if (frames_cap) *frames_cap = ctx->frames_cap;
+}
+
+void ga::ring_release_to(ga_ctx *ctx, uint64_t off)
+{
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    for (auto &s : ctx->slots) if (s.busy) return;
+    const uint64_t head = ctx->ring_head.load(std::memory_order_acquire);
+    if (off > head) off = head;
+    if (off > ctx->ring_tail.load(std::memory_order_relaxed)) ctx->ring_tail.store(off, std::memory_order_release);
+}
+
+int ga::submit_impl(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *ticket, uint32_t *bad_index)
+{
     GA_GUARD_BEGIN
+    if (bad_index) *bad_index = 0xffffffffu;
     if (!ctx || !ticket || (n && !msgs)) { set_error("ga_submit: NULL argument"); return GA_ERR_ARG; }
     if (n > ctx->cfg.max_batch_msgs) { set_error("ga_submit: %u messages exceed max_batch_msgs %u", n, ctx->cfg.max_batch_msgs); return GA_ERR_OVERFLOW; }
     std::lock_guard<std::mutex> lk(ctx->mu);
     int rc = set_device(ctx);
     if (rc) return rc;
-    Slot *slot = nullptr;
-    for (auto &s : ctx->slots) if (!s.busy) { slot = &s; break; }
-    if (!slot) { set_error("ga_submit: %u tickets already in flight", ctx->cfg.max_inflight); return GA_ERR_STATE; }
+    // slots are used round-robin (ticket t lives in slot (t-1) % max_inflight), so the pinned result
+    // buffers a ga_wait_view handed out are not written again before ticket t + max_inflight is submitted
+    Slot *slot = &ctx->slots[(ctx->next_ticket - 1) % ctx->slots.size()];
+    if (slot->busy) { set_error("ga_submit: %u tickets already in flight", ctx->cfg.max_inflight); return GA_ERR_STATE; }
 
     const uint64_t size = ctx->cfg.ring_bytes;
     const uint64_t arena = ctx->cfg.arena_samples, wake_cap = ctx->cfg.wake_samples_max;
@@ -362,6 +386,7 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
     uint32_t n_chains = 0;
     ga_rdesc *rdescs = slot->h_rdesc;
     const uint64_t stamp = ctx->next_ticket;      // marks streams already seen in THIS batch
+    ctx->touched.clear();
     // equal-sized chunks copied into the ring back to back (a batch tick) can be staged by one
     // 2-D TMA copy per 32 messages instead of one bulk copy per message
     bool uniform = n > 0;
@@ -379,6 +404,7 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
         if (i == 0) { phys0 = phys; ustride = need; }
         else if (uniform) uniform = (m.nbytes == msgs[0].nbytes) && (phys == phys0 + i * ustride);
         StreamState &st = streams[m.stream_id];
+        if (st.stamp != stamp) ctx->touched.emplace_back(m.stream_id, st.stamp);   // first message of the stream in this batch
         if (m.flags & GA_MSG_FIRST) {
             // a new utterance reuses the stream's arena from its start while the batch's kernel may
             // still be writing the old utterance's chunks there: it has to wait for the next batch
@@ -494,14 +520,17 @@ extern "C" int ga_submit(ga_ctx *ctx, const ga_msg *msgs, uint32_t n, uint64_t *
                 ns = (n1 >= 3 * mf + 3) ? (n1 - 3 * mf - 3) / 3 + 1 : 0;
             }
             if (fmt48 || utter) ctx->batch_stamp[m.stream_id] = 0;
-            st.stamp = 0;
             ((m.flags & GA_MSG_WAKE) ? st.wake_n : st.speech_n) -= ns;
             if (m.flags & GA_MSG_FIRST) { st = resets.back().before; resets.pop_back(); }
         }
+        // every stream this batch touched (the refused message's included) gets back the ticket that
+        // last appended to it: a later GA_MSG_FIRST / ga_stream_reset must still fence against that
+        // ticket if it is in flight, and the failed batch's ticket number will be used again
+        for (auto it = ctx->touched.rbegin(); it != ctx->touched.rend(); ++it) streams[it->first].stamp = it->second;
+        ctx->touched.clear();
     };
     if (err) {
-        if (i < n && msgs[i].stream_id < max_streams && streams[msgs[i].stream_id].stamp == stamp)
-            streams[msgs[i].stream_id].stamp = 0;      // the refused message itself (undo covers those before it)
+        if (bad_index && i < n) *bad_index = i;     // the refusal is about message i (and so about its stream)
         undo(i);
         return err;
     }
@@ -696,9 +725,8 @@ extern "C" int ga_submit_ticks(ga_ctx *ctx, uint64_t ring_offset, uint32_t n_tic
     if (convert && arena > 0xffffffffull) { set_error("ga_submit_ticks: arena_samples beyond 2^32; use ga_submit"); return GA_ERR_STATE; }
     int rc = set_device(ctx);
     if (rc) return rc;
-    Slot *slot = nullptr;
-    for (auto &s : ctx->slots) if (!s.busy) { slot = &s; break; }
-    if (!slot) { set_error("ga_submit_ticks: %u tickets already in flight", ctx->cfg.max_inflight); return GA_ERR_STATE; }
+    Slot *slot = &ctx->slots[(ctx->next_ticket - 1) % ctx->slots.size()];      // round-robin, as in ga_submit
+    if (slot->busy) { set_error("ga_submit_ticks: %u tickets already in flight", ctx->cfg.max_inflight); return GA_ERR_STATE; }
 
     const uint64_t size = ctx->cfg.ring_bytes;
     const uint64_t stride = (static_cast<uint64_t>(chunk_bytes) + 15u) & ~15ull;

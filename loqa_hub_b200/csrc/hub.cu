@@ -14,9 +14,20 @@
 // rooms arbitrate concurrently.  With a single group the behaviour is the reference's.
 // Time is injected (now_us) instead of read from a clock, and the timer goroutine (:494-502) is
 // ga_hub_poll: every window whose duration has elapsed is arbitrated in ONE ga_arbitrate call.
+//
+// Locking.  The reference takes its global streamsMutex for EVERY chunk (:1000-1004).  Here the hub
+// mutex guards the registry and the windows only: a wake-word chunk takes it to start / join its
+// group's window (the first ~15 of an utterance's 250 chunks); a speech chunk takes no hub-wide
+// lock at all.  The chunk's bytes are copied into the pinned ring outside any lock, and the message
+// is published on a per-GPU multi-producer queue whose sequence numbers are handed out together
+// with the ring reservation (a mutex per GPU held for those two operations only), so that the
+// flush always takes a prefix of the queue that is complete both in arrival order and in ring
+// offsets — the ring is released by offset when a ticket is waited.
 #include <algorithm>
+#include <atomic>
 #include <cstring>
 #include <map>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <unordered_map>
@@ -27,17 +38,20 @@
 
 namespace {
 
-struct Relay {                       // RelayStream :44-53
+struct Relay {                       // RelayStream :44-53; lives in a fixed table, index = shard * max_slots + slot
     std::string id;
     uint32_t group = 0;
     uint32_t shard = 0;              // which GPU's context holds the relay's audio
     uint32_t slot = 0;               // ga_ctx stream slot there: WakeWordSignal / SpeechAudio live on the GPU
-    int status = GA_RELAY_CONNECTED; // :56-63
+    std::atomic<int> status{GA_RELAY_CONNECTED};   // :56-63 (read by the relay's own chunk path without the hub lock)
     double signal_strength = 0.0;    // :50
     bool cancel_closed = false;      // close(relay.CancelChannel) :561
-    bool in_active_streams = false;  // as.activeStreams[relayID] exists (:91)
-    bool first_chunk = true;
+    std::atomic<bool> in_active_streams{false};    // as.activeStreams[relayID] exists (:91)
+    std::atomic<bool> first_chunk{true};
     uint64_t window = 0;             // window it last joined (0 = none)
+    std::atomic<uint32_t> gen{0};    // bumped when the slot changes hands: stale handles and queued chunks are refused
+    bool alive = false;
+    uint64_t dropped_chunks = 0;     // chunks the flush had to drop (sample arena full)
 };
 
 struct Window {                      // ArbitrationWindow :66-73
@@ -50,6 +64,27 @@ struct Window {                      // ArbitrationWindow :66-73
     std::string winner;              // WinnerID
 };
 
+struct QMsg {
+    ga_msg m;
+    uint32_t gen;                    // the slot's generation when the chunk arrived
+};
+
+struct QEntry {
+    QMsg v;
+    std::atomic<uint64_t> ready{0};  // sequence number + 1 once v is published
+};
+
+// Chunks pushed since the last flush, per GPU: bounded multi-producer / single-consumer queue.
+struct ShardQueue {
+    std::mutex claim;                // held for {ring reservation, sequence number} only
+    uint64_t tail = 0;               // next sequence number (under claim)
+    std::atomic<uint64_t> head{0};   // first sequence number the flush has not taken yet
+    std::unique_ptr<QEntry[]> q;
+    uint64_t cap = 0;                // power of two
+    std::vector<QMsg> carry;         // taken off the queue but not submitted (flush only)
+    uint64_t taken_end = 0;          // ring offset up to which the flush has taken chunks
+};
+
 }  // namespace
 
 struct ga_hub {
@@ -58,23 +93,59 @@ struct ga_hub {
     std::vector<ga_ctx *> ctxs;
     ga_cluster *cluster = nullptr;
     uint64_t window_duration_us = 300000;                 // arbitrationWindowDuration, 300 ms (:243)
-    std::unordered_map<std::string, Relay> relays;
+    std::unique_ptr<Relay[]> table;                       // n_shards * max_slots entries, never moved
+    std::unordered_map<std::string, uint32_t> by_id;      // relay id -> table index
     std::map<uint64_t, Window> windows;                   // every window ever opened and not yet dropped
     std::unordered_map<uint32_t, uint64_t> group_window;  // as.arbitrationWindow per group (absent = nil)
     std::vector<std::vector<uint32_t>> free_slots;        // per shard
     std::vector<uint32_t> next_slot;
     uint32_t max_slots = 0;                               // stream slots per shard
+    uint32_t n_shards = 1;
     uint64_t next_window = 1;
-    std::vector<std::vector<ga_msg>> pending;             // per shard: chunks pushed since the last flush
-    std::mutex mu;
+    std::unique_ptr<ShardQueue[]> queues;                 // per shard
+    std::mutex mu;                                        // registry + windows
+    std::mutex flush_mu;                                  // one flush at a time
 };
 
 using namespace ga;
 
 static Relay *find_relay(ga_hub *h, const char *id)
 {
-    auto it = h->relays.find(id);
-    return it == h->relays.end() ? nullptr : &it->second;
+    auto it = h->by_id.find(id);
+    return it == h->by_id.end() ? nullptr : &h->table[it->second];
+}
+
+static inline uint64_t handle_of(const ga_hub *h, const Relay *r)
+{
+    return (static_cast<uint64_t>(r->gen.load(std::memory_order_relaxed)) << 32) | (r->shard * h->max_slots + r->slot);
+}
+
+static Relay *relay_of_handle(ga_hub *h, uint64_t handle)
+{
+    const uint32_t idx = static_cast<uint32_t>(handle), gen = static_cast<uint32_t>(handle >> 32);
+    if (idx >= h->n_shards * h->max_slots) return nullptr;
+    Relay *r = &h->table[idx];
+    return r->gen.load(std::memory_order_acquire) == gen && (gen & 1u) ? r : nullptr;     // odd generation = slot in use
+}
+
+static int hub_alloc(ga_hub *h, uint32_t n_shards, uint32_t max_slots, uint64_t window_duration_us)
+{
+    h->max_slots = max_slots;
+    h->n_shards = n_shards;
+    h->free_slots.resize(n_shards);
+    h->next_slot.assign(n_shards, 0);
+    h->table.reset(new Relay[static_cast<size_t>(n_shards) * max_slots]);
+    h->queues.reset(new ShardQueue[n_shards]);
+    for (uint32_t sh = 0; sh < h->ctxs.size(); sh++) {
+        uint32_t max_batch = 0;
+        ga::ctx_limits(h->ctxs[sh], &max_batch, nullptr);
+        uint64_t cap = 1024;
+        while (cap < 4ull * max_batch) cap <<= 1;           // four full batches may wait for a flush
+        h->queues[sh].cap = cap;
+        h->queues[sh].q.reset(new QEntry[cap]);
+    }
+    if (window_duration_us) h->window_duration_us = window_duration_us;
+    return GA_OK;
 }
 
 extern "C" int ga_hub_create(ga_ctx *ctx, uint32_t max_streams, uint64_t window_duration_us, ga_hub **out)
@@ -83,13 +154,10 @@ extern "C" int ga_hub_create(ga_ctx *ctx, uint32_t max_streams, uint64_t window_
     // ctx may be NULL: the registry and the window bookkeeping then work on their own (that is how
     // the CPU-only tests run them); everything that needs samples reports GA_ERR_STATE
     if (!out || max_streams == 0) { set_error("ga_hub_create: bad argument"); return GA_ERR_ARG; }
-    ga_hub *h = new (std::nothrow) ga_hub;
-    if (!h) { set_error("ga_hub_create: out of memory"); return GA_ERR_NOMEM; }
+    std::unique_ptr<ga_hub> h(new ga_hub);
     if (ctx) h->ctxs.push_back(ctx);
-    h->max_slots = max_streams;
-    h->free_slots.resize(1); h->next_slot.assign(1, 0); h->pending.resize(1);
-    if (window_duration_us) h->window_duration_us = window_duration_us;
-    *out = h;
+    hub_alloc(h.get(), 1, max_streams, window_duration_us);
+    *out = h.release();
     return GA_OK;
     GA_GUARD_END
 }
@@ -101,14 +169,11 @@ extern "C" int ga_hub_create_cluster(ga_cluster *cluster, uint32_t max_streams_p
     GA_GUARD_BEGIN
     if (!out || !cluster || max_streams_per_shard == 0) { set_error("ga_hub_create_cluster: bad argument"); return GA_ERR_ARG; }
     const uint32_t n = ga_cluster_size(cluster);
-    ga_hub *h = new (std::nothrow) ga_hub;
-    if (!h) { set_error("ga_hub_create_cluster: out of memory"); return GA_ERR_NOMEM; }
+    std::unique_ptr<ga_hub> h(new ga_hub);
     for (uint32_t i = 0; i < n; i++) h->ctxs.push_back(ga_cluster_context(cluster, i));
     h->cluster = cluster;
-    h->max_slots = max_streams_per_shard;
-    h->free_slots.resize(n); h->next_slot.assign(n, 0); h->pending.resize(n);
-    if (window_duration_us) h->window_duration_us = window_duration_us;
-    *out = h;
+    hub_alloc(h.get(), n, max_streams_per_shard, window_duration_us);
+    *out = h.release();
     return GA_OK;
     GA_GUARD_END
 }
@@ -117,7 +182,7 @@ extern "C" void ga_hub_destroy(ga_hub *h) { delete h; }
 
 // A relay device opened its gRPC stream (StreamAudio :926).  It is known to the hub but not yet
 // in activeStreams — the reference only adds it there when it starts or joins a window.
-static int connect_relay(ga_hub *h, const char *relay_id, uint32_t group, uint32_t shard, uint32_t *slot)
+static int connect_relay(ga_hub *h, const char *relay_id, uint32_t group, uint32_t shard, uint32_t *slot, uint64_t *handle)
 {
     std::lock_guard<std::mutex> lk(h->mu);
     Relay *r = find_relay(h, relay_id);
@@ -127,13 +192,18 @@ static int connect_relay(ga_hub *h, const char *relay_id, uint32_t group, uint32
         if (!fs.empty()) { s = fs.back(); fs.pop_back(); }
         else if (h->next_slot[shard] < h->max_slots) s = h->next_slot[shard]++;
         else { set_error("ga_hub_connect: all %u stream slots of shard %u are in use", h->max_slots, shard); return GA_ERR_OVERFLOW; }
-        Relay nr;
-        nr.id = relay_id; nr.slot = s; nr.shard = shard;
-        r = &h->relays.emplace(relay_id, nr).first->second;
+        const uint32_t idx = shard * h->max_slots + s;
+        r = &h->table[idx];
+        r->id = relay_id; r->slot = s; r->shard = shard;
+        r->status.store(GA_RELAY_CONNECTED); r->signal_strength = 0.0; r->cancel_closed = false;
+        r->in_active_streams.store(false); r->window = 0; r->alive = true; r->dropped_chunks = 0;
+        r->gen.store(r->gen.load() + 1, std::memory_order_release);       // even -> odd: in use
+        h->by_id.emplace(relay_id, idx);
     }
     r->group = group;                 // a known relay keeps its shard and slot: its audio lives there
-    r->first_chunk = true;
+    r->first_chunk.store(true);
     if (slot) *slot = r->slot;
+    if (handle) *handle = handle_of(h, r);
     return GA_OK;
 }
 
@@ -142,8 +212,7 @@ extern "C" int ga_hub_connect(ga_hub *h, const char *relay_id, uint32_t group, u
     GA_GUARD_BEGIN
     if (!h || !relay_id) { set_error("ga_hub_connect: bad argument"); return GA_ERR_ARG; }
     // a collision group lives on shard group % nGPU, so its windows normally stay on one GPU
-    const uint32_t n = static_cast<uint32_t>(h->free_slots.size());
-    return connect_relay(h, relay_id, group, group % n, slot);
+    return connect_relay(h, relay_id, group, group % h->n_shards, slot, nullptr);
     GA_GUARD_END
 }
 
@@ -153,8 +222,20 @@ extern "C" int ga_hub_connect_on(ga_hub *h, const char *relay_id, uint32_t group
 {
     GA_GUARD_BEGIN
     if (!h || !relay_id) { set_error("ga_hub_connect_on: bad argument"); return GA_ERR_ARG; }
-    if (shard >= h->free_slots.size()) { set_error("ga_hub_connect_on: shard %u of %zu", shard, h->free_slots.size()); return GA_ERR_ARG; }
-    return connect_relay(h, relay_id, group, shard, slot);
+    if (shard >= h->n_shards) { set_error("ga_hub_connect_on: shard %u of %u", shard, h->n_shards); return GA_ERR_ARG; }
+    return connect_relay(h, relay_id, group, shard, slot, nullptr);
+    GA_GUARD_END
+}
+
+extern "C" int ga_hub_relay_handle(ga_hub *h, const char *relay_id, uint64_t *handle)
+{
+    GA_GUARD_BEGIN
+    if (!h || !relay_id || !handle) { set_error("ga_hub_relay_handle: bad argument"); return GA_ERR_ARG; }
+    std::lock_guard<std::mutex> lk(h->mu);
+    Relay *r = find_relay(h, relay_id);
+    if (!r) { set_error("ga_hub_relay_handle: unknown relay %s", relay_id); return GA_ERR_STATE; }
+    *handle = handle_of(h, r);
+    return GA_OK;
     GA_GUARD_END
 }
 
@@ -233,21 +314,42 @@ extern "C" int ga_hub_join_window(ga_hub *h, const char *relay_id, uint64_t now_
     GA_GUARD_END
 }
 
+// The chunk's bytes go into the pinned ring and the message onto the GPU's queue.  Only the ring
+// reservation and the sequence number are taken under the queue's mutex; the copy is not.
+static int enqueue_chunk(ga_hub *h, Relay *r, const uint8_t *audio, uint32_t nbytes, uint32_t flags)
+{
+    ShardQueue &q = h->queues[r->shard];
+    void *dst = nullptr;
+    uint64_t off = 0, seq = 0;
+    {
+        std::lock_guard<std::mutex> lk(q.claim);
+        if (q.tail - q.head.load(std::memory_order_acquire) >= q.cap) {
+            set_error("ga_hub_on_chunk: %llu chunks are waiting for a flush on GPU %u", (unsigned long long)q.cap, r->shard);
+            return GA_ERR_RING_FULL;
+        }
+        int rc = ga_ring_reserve(h->ctxs[r->shard], nbytes, &dst, &off);
+        if (rc) return rc;
+        seq = q.tail++;
+    }
+    if (nbytes) std::memcpy(dst, audio, nbytes);
+    QEntry &e = q.q[seq & (q.cap - 1)];
+    e.v.m = ga_msg{};
+    e.v.m.ring_offset = off; e.v.m.nbytes = nbytes; e.v.m.stream_id = r->slot; e.v.m.flags = flags;
+    e.v.gen = r->gen.load(std::memory_order_relaxed);
+    e.ready.store(seq + 1, std::memory_order_release);
+    return GA_OK;
+}
+
 // One received AudioChunk: the body of the StreamAudio loop, :939-1041.  keep_stream = 0 is the
 // reference's `return nil` (the handler ends and the relay's stream is closed).
-extern "C" int ga_hub_on_chunk(ga_hub *h, const char *relay_id, const uint8_t *audio, uint32_t nbytes,
-                               int is_wake_word, int is_end_of_speech, uint64_t now_us, int *keep_stream)
+static int on_chunk(ga_hub *h, Relay *r, const uint8_t *audio, uint32_t nbytes, int is_wake_word, int is_end_of_speech,
+                    uint64_t now_us, int *keep_stream)
 {
-    GA_GUARD_BEGIN
-    if (!h || !relay_id || (nbytes && !audio)) { set_error("ga_hub_on_chunk: bad argument"); return GA_ERR_ARG; }
-    std::lock_guard<std::mutex> lk(h->mu);
-    Relay *r = find_relay(h, relay_id);
-    if (!r) { set_error("ga_hub_on_chunk: relay %s is not connected", relay_id); return GA_ERR_STATE; }
-    if (h->ctxs.empty()) { set_error("ga_hub_on_chunk: this hub has no GPU context"); return GA_ERR_STATE; }
     if (keep_stream) *keep_stream = 1;
     bool ingest = false;
     if (is_wake_word) {                                           // :962
         ingest = true;                                            // :964-965 convert + append to wakeWordBuffer
+        std::lock_guard<std::mutex> lk(h->mu);                    // the window registry: wake-word chunks only
         if (h->group_window.find(r->group) == h->group_window.end()) {
             start_window(h, r, now_us);                           // :972-980
         } else if (!join_window(h, r, now_us)) {                  // :983-995 too late
@@ -255,99 +357,174 @@ extern "C" int ga_hub_on_chunk(ga_hub *h, const char *relay_id, const uint8_t *a
             return GA_OK;
         }
     } else {
-        ingest = r->in_active_streams;                            // :1000-1004: only relays in activeStreams keep speech
+        ingest = r->in_active_streams.load(std::memory_order_acquire);   // :1000-1004: only relays in activeStreams keep speech
     }
     if (ingest) {
-        void *dst = nullptr;
-        uint64_t off = 0;
-        int rc = ga_ring_reserve(h->ctxs[r->shard], nbytes, &dst, &off);
-        if (rc) return rc;
-        if (nbytes) std::memcpy(dst, audio, nbytes);
-        ga_msg m{};
-        m.ring_offset = off; m.nbytes = nbytes; m.stream_id = r->slot;
-        m.flags = (is_wake_word ? GA_MSG_WAKE : 0u) | (is_end_of_speech ? GA_MSG_EOS : 0u) |
-                  (r->first_chunk ? GA_MSG_FIRST : 0u);
-        r->first_chunk = false;
-        h->pending[r->shard].push_back(m);
+        const bool first = r->first_chunk.exchange(false);
+        int rc = enqueue_chunk(h, r, audio, nbytes,
+                               (is_wake_word ? GA_MSG_WAKE : 0u) | (is_end_of_speech ? GA_MSG_EOS : 0u) | (first ? GA_MSG_FIRST : 0u));
+        if (rc) { if (first) r->first_chunk.store(true); return rc; }
     }
     if (is_end_of_speech) {                                       // :1008-1041
-        const bool active = r->in_active_streams && (r->status == GA_RELAY_WINNER || r->status == GA_RELAY_CONNECTED ||
-                                                     r->status == GA_RELAY_CONTENDING);
+        const int st = r->status.load(std::memory_order_acquire);
+        const bool active = r->in_active_streams.load(std::memory_order_acquire) &&
+                            (st == GA_RELAY_WINNER || st == GA_RELAY_CONNECTED || st == GA_RELAY_CONTENDING);
         if (!active && keep_stream) *keep_stream = 0;             // :1018-1021
     }
     return GA_OK;
+}
+
+extern "C" int ga_hub_on_chunk(ga_hub *h, const char *relay_id, const uint8_t *audio, uint32_t nbytes,
+                               int is_wake_word, int is_end_of_speech, uint64_t now_us, int *keep_stream)
+{
+    GA_GUARD_BEGIN
+    if (!h || !relay_id || (nbytes && !audio)) { set_error("ga_hub_on_chunk: bad argument"); return GA_ERR_ARG; }
+    Relay *r;
+    {
+        std::lock_guard<std::mutex> lk(h->mu);      // name lookup only; ga_hub_on_chunk_h skips it
+        r = find_relay(h, relay_id);
+    }
+    if (!r) { set_error("ga_hub_on_chunk: relay %s is not connected", relay_id); return GA_ERR_STATE; }
+    if (h->ctxs.empty()) { set_error("ga_hub_on_chunk: this hub has no GPU context"); return GA_ERR_STATE; }
+    return on_chunk(h, r, audio, nbytes, is_wake_word, is_end_of_speech, now_us, keep_stream);
     GA_GUARD_END
 }
 
-// The batch tick: everything pushed since the last flush goes through ONE ga_submit per GPU, all
-// GPUs working at the same time.
+extern "C" int ga_hub_on_chunk_h(ga_hub *h, uint64_t handle, const uint8_t *audio, uint32_t nbytes,
+                                 int is_wake_word, int is_end_of_speech, uint64_t now_us, int *keep_stream)
+{
+    GA_GUARD_BEGIN
+    if (!h || (nbytes && !audio)) { set_error("ga_hub_on_chunk_h: bad argument"); return GA_ERR_ARG; }
+    Relay *r = relay_of_handle(h, handle);
+    if (!r) { set_error("ga_hub_on_chunk_h: stale or unknown relay handle"); return GA_ERR_STATE; }
+    if (h->ctxs.empty()) { set_error("ga_hub_on_chunk_h: this hub has no GPU context"); return GA_ERR_STATE; }
+    return on_chunk(h, r, audio, nbytes, is_wake_word, is_end_of_speech, now_us, keep_stream);
+    GA_GUARD_END
+}
+
+// The batch tick: everything pushed since the last flush goes through ga_submit, one batch per GPU
+// at a time, all GPUs working at the same time.  A batch is cut where a relay restarts an utterance
+// after chunks of its previous one, and at the context's max_batch_msgs.  A chunk the context
+// refuses for its stream's sake (the relay's sample arena is full — the reference appends without
+// bound, :965 / :1002) takes that relay's chunks out of the batch and the rest goes ahead; the call
+// then returns GA_ERR_OVERFLOW after everything else has been ingested.
 extern "C" int ga_hub_flush(ga_hub *h, uint32_t *n_msgs)
 {
     GA_GUARD_BEGIN
     if (!h) { set_error("ga_hub_flush: NULL hub"); return GA_ERR_ARG; }
     if (h->ctxs.empty()) { set_error("ga_hub_flush: this hub has no GPU context"); return GA_ERR_STATE; }
+    std::lock_guard<std::mutex> flk(h->flush_mu);
     struct Work {
         std::vector<ga_msg> batch;
-        std::vector<size_t> cuts;     // ends of the sub-batches
-        size_t next = 0, lo = 0;      // next sub-batch to submit, first message not yet submitted
+        size_t lo = 0;                // first message not yet submitted
+        uint32_t max_batch = 0;
+        size_t limit = 0;             // current sub-batch size limit (halved when the context refuses a batch as a whole)
         uint64_t ticket = 0;
-        bool inflight = false, done = false;
+        uint64_t end_off = 0;         // ring offset behind the last chunk taken
+        bool inflight = false, done = false, failed = false;
     };
-    const uint32_t n_sh = static_cast<uint32_t>(h->ctxs.size());
+    const uint32_t n_sh = h->n_shards;
     std::vector<Work> work(n_sh);
-    {
-        std::lock_guard<std::mutex> lk(h->mu);   // only to take the queues: chunks keep arriving while the GPUs work
-        for (uint32_t sh = 0; sh < n_sh; sh++) work[sh].batch.swap(h->pending[sh]);
-    }
-    uint32_t total = 0;
-    for (auto &w : work) {
+    uint32_t total = 0, dropped = 0, kept_back = 0;
+    for (uint32_t sh = 0; sh < n_sh; sh++) {
+        ShardQueue &q = h->queues[sh];
+        Work &w = work[sh];
+        ga::ctx_limits(h->ctxs[sh], &w.max_batch, nullptr);
+        w.limit = w.max_batch ? w.max_batch : 1;
+        std::vector<QMsg> taken;
+        taken.swap(q.carry);
+        uint64_t head = q.head.load(std::memory_order_relaxed);
+        for (;; head++) {               // the published prefix: complete in arrival order and in ring offsets
+            QEntry &e = q.q[head & (q.cap - 1)];
+            if (e.ready.load(std::memory_order_acquire) != head + 1) break;
+            taken.push_back(e.v);
+        }
+        q.head.store(head, std::memory_order_release);
+        for (const QMsg &t : taken) {
+            const uint64_t end = t.m.ring_offset + ((static_cast<uint64_t>(t.m.nbytes) + 15u) & ~15ull);
+            if (end > q.taken_end) q.taken_end = end;
+            // chunks of a relay that was cleaned up before the flush go with it: the slot may have a new owner
+            if (h->table[sh * h->max_slots + t.m.stream_id].gen.load(std::memory_order_acquire) != t.gen) continue;
+            w.batch.push_back(t.m);
+        }
+        w.end_off = q.taken_end;
         total += static_cast<uint32_t>(w.batch.size());
         w.done = w.batch.empty();
-        // A relay that finished an utterance and started the next one within one tick has chunks
-        // of both in the queue; ga_submit wants the restart in a later batch than the old chunks,
-        // so the queue is cut there (rare: normally one submit per GPU).
+    }
+    // end of the sub-batch that starts at w.lo
+    auto next_cut = [](const Work &w) {
+        size_t hi = std::min(w.batch.size(), w.lo + w.limit);
         bool any_first = false;
-        for (size_t k = 1; k < w.batch.size() && !any_first; k++) any_first = (w.batch[k].flags & GA_MSG_FIRST) != 0;
+        for (size_t k = w.lo + 1; k < hi && !any_first; k++) any_first = (w.batch[k].flags & GA_MSG_FIRST) != 0;
         if (any_first) {
             std::unordered_set<uint32_t> seen;
-            for (size_t k = 0; k < w.batch.size(); k++) {
-                if ((w.batch[k].flags & GA_MSG_FIRST) && seen.count(w.batch[k].stream_id)) { w.cuts.push_back(k); seen.clear(); }
+            for (size_t k = w.lo; k < hi; k++) {
+                if ((w.batch[k].flags & GA_MSG_FIRST) && seen.count(w.batch[k].stream_id)) { hi = k; break; }
                 seen.insert(w.batch[k].stream_id);
             }
         }
-        w.cuts.push_back(w.batch.size());
-    }
+        return hi;
+    };
     int first_err = GA_OK;
-    uint32_t lost = 0;
     for (bool busy = true; busy;) {
         busy = false;
-        for (uint32_t sh = 0; sh < n_sh; sh++) {            // round k: the k-th sub-batch of every GPU
+        for (uint32_t sh = 0; sh < n_sh; sh++) {            // round k: the next sub-batch of every GPU
             Work &w = work[sh];
             if (w.done) continue;
-            const size_t hi = w.cuts[w.next];
-            const int rc = ga_submit(h->ctxs[sh], w.batch.data() + w.lo, static_cast<uint32_t>(hi - w.lo), &w.ticket);
-            if (rc) {                                       // nothing of [lo, end) was queued: it stays pending, in order
-                std::lock_guard<std::mutex> lk(h->mu);
-                h->pending[sh].insert(h->pending[sh].begin(), w.batch.begin() + w.lo, w.batch.end());
-                lost += static_cast<uint32_t>(w.batch.size() - w.lo);
+            for (;;) {
+                const size_t hi = next_cut(w);
+                uint32_t bad = 0xffffffffu;
+                const int rc = ga::submit_impl(h->ctxs[sh], w.batch.data() + w.lo, static_cast<uint32_t>(hi - w.lo), &w.ticket, &bad);
+                if (rc == GA_OK) { w.inflight = true; w.lo = hi; w.limit = w.max_batch ? w.max_batch : 1; break; }
+                if (rc == GA_ERR_OVERFLOW && bad == 0xffffffffu && hi - w.lo > 1) {
+                    w.limit = (hi - w.lo) / 2;                  // the batch as a whole is too big (frame records): halve it
+                    continue;
+                }
+                if ((rc == GA_ERR_OVERFLOW || rc == GA_ERR_ARG) && bad != 0xffffffffu) {
+                    // one relay's chunk cannot be taken: drop that relay's chunks, keep everybody else's
+                    const uint32_t slot = w.batch[w.lo + bad].stream_id;
+                    const size_t before = w.batch.size();
+                    w.batch.erase(std::remove_if(w.batch.begin() + w.lo, w.batch.end(),
+                                                 [slot](const ga_msg &m) { return m.stream_id == slot; }), w.batch.end());
+                    const uint32_t k = static_cast<uint32_t>(before - w.batch.size());
+                    dropped += k;
+                    {
+                        std::lock_guard<std::mutex> lk(h->mu);
+                        Relay &r = h->table[sh * h->max_slots + slot];
+                        r.dropped_chunks += k;
+                        r.in_active_streams.store(false);       // no more speech is kept for it (as for a relay outside activeStreams)
+                    }
+                    if (!first_err) first_err = GA_ERR_OVERFLOW;
+                    if (w.lo == w.batch.size()) { w.done = !w.inflight; break; }
+                    continue;                                   // the same sub-batch without that relay
+                }
+                // not about one stream (CUDA failure, pipeline full …): keep the rest for the next flush, in order
+                ShardQueue &q = h->queues[sh];
+                for (size_t k = w.lo; k < w.batch.size(); k++)
+                    q.carry.push_back(QMsg{w.batch[k], h->table[sh * h->max_slots + w.batch[k].stream_id].gen.load()});
+                kept_back += static_cast<uint32_t>(w.batch.size() - w.lo);
+                w.failed = true;
                 w.done = true;
-                if (!first_err) first_err = rc;             // a failing GPU does not hold the others back
-                continue;
+                if (!first_err || first_err == GA_ERR_OVERFLOW) first_err = rc;     // a failing GPU does not hold the others back
+                break;
             }
-            w.inflight = true;
-            w.lo = hi;
-            w.next++;
         }
         for (uint32_t sh = 0; sh < n_sh; sh++) {
             Work &w = work[sh];
             if (!w.inflight) continue;
             w.inflight = false;
             const int rc = ga_wait_view(h->ctxs[sh], w.ticket, nullptr, nullptr, nullptr, nullptr);
-            if (rc) { w.done = true; if (!first_err) first_err = rc; continue; }
-            if (w.next == w.cuts.size()) w.done = true; else busy = true;
+            if (rc) { w.done = true; w.failed = true; if (!first_err || first_err == GA_ERR_OVERFLOW) first_err = rc; continue; }
+            if (w.lo == w.batch.size()) w.done = true; else if (!w.done) busy = true;
         }
     }
-    if (n_msgs) *n_msgs = total - lost;
+    // chunks that were dropped never reach a ticket, so no wait releases their ring space: once a
+    // GPU's whole prefix has been dealt with, everything up to its end is free
+    for (uint32_t sh = 0; sh < n_sh; sh++)
+        if (!work[sh].failed && work[sh].end_off) ga::ring_release_to(h->ctxs[sh], work[sh].end_off);
+    if (n_msgs) *n_msgs = total - dropped - kept_back;
+    if (first_err == GA_ERR_OVERFLOW && dropped)
+        set_error("ga_hub_flush: dropped %u chunk(s) of relays whose sample arena is full; everything else was ingested", dropped);
     return first_err;
     GA_GUARD_END
 }
@@ -366,17 +543,17 @@ static int arbitrate_windows(ga_hub *h, const std::vector<uint64_t> &ids)
         if (it == h->windows.end() || !it->second.is_active) continue;    // :508-511 already arbitrated
         Window &w = it->second;
         for (auto &rid : w.relays) {
-            auto rit = h->relays.find(rid);
-            if (rit == h->relays.end()) {
+            Relay *rp = find_relay(h, rid.c_str());
+            if (!rp) {
                 // the relay was cleaned up (cleanupRelay :916-923) while its window was open: its stream
                 // slot is gone, so it takes part as a member that is not contending
                 sid.push_back(0); shard.push_back(0); st_in.push_back(GA_RELAY_CANCELLED); scores.push_back(0.0);
                 continue;
             }
-            Relay &r = rit->second;
+            Relay &r = *rp;
             sid.push_back(r.slot);
             shard.push_back(r.shard);
-            st_in.push_back(static_cast<uint8_t>(r.status));
+            st_in.push_back(static_cast<uint8_t>(r.status.load()));
             scores.push_back(r.signal_strength);                          // untouched for skipped relays (:522-524)
         }
         seg.push_back(static_cast<uint32_t>(sid.size()));
@@ -395,9 +572,9 @@ static int arbitrate_windows(ga_hub *h, const std::vector<uint64_t> &ids)
     for (size_t k = 0; k < ws.size(); k++) {
         Window &w = *ws[k];
         for (uint32_t m = seg[k]; m < seg[k + 1]; m++) {
-            auto rit = h->relays.find(w.relays[m - seg[k]]);
-            if (rit == h->relays.end()) continue;                         // cleaned up meanwhile: nothing to update
-            Relay &r = rit->second;
+            Relay *rp = find_relay(h, w.relays[m - seg[k]].c_str());
+            if (!rp) continue;                                            // cleaned up meanwhile: nothing to update
+            Relay &r = *rp;
             r.signal_strength = scores[m];                                // :528
             r.status = st_out[m];                                         // :553-571
             if (st_out[m] == GA_RELAY_CANCELLED) r.cancel_closed = true;  // :561 close(relay.CancelChannel)
@@ -472,7 +649,7 @@ extern "C" int ga_hub_relay_info(ga_hub *h, const char *relay_id, int *status, d
     std::lock_guard<std::mutex> lk(h->mu);
     Relay *r = find_relay(h, relay_id);
     if (!r) { set_error("ga_hub_relay_info: unknown relay %s", relay_id); return GA_ERR_STATE; }
-    if (status) *status = r->status;
+    if (status) *status = r->status.load();
     if (signal_strength) *signal_strength = r->signal_strength;
     if (cancel_closed) *cancel_closed = r->cancel_closed ? 1 : 0;
     if (slot) *slot = r->slot;
@@ -487,8 +664,9 @@ extern "C" int ga_hub_is_relay_active(ga_hub *h, const char *relay_id)
     if (!h || !relay_id) return 0;
     std::lock_guard<std::mutex> lk(h->mu);
     Relay *r = find_relay(h, relay_id);
-    if (!r || !r->in_active_streams) return 0;
-    return (r->status == GA_RELAY_WINNER || r->status == GA_RELAY_CONNECTED || r->status == GA_RELAY_CONTENDING) ? 1 : 0;
+    if (!r || !r->in_active_streams.load()) return 0;
+    const int st = r->status.load();
+    return (st == GA_RELAY_WINNER || st == GA_RELAY_CONNECTED || st == GA_RELAY_CONTENDING) ? 1 : 0;
     GA_GUARD_END
 }
 
@@ -529,15 +707,19 @@ extern "C" int ga_hub_cleanup_relay(ga_hub *h, const char *relay_id)
     GA_GUARD_BEGIN
     if (!h || !relay_id) { set_error("ga_hub_cleanup_relay: bad argument"); return GA_ERR_ARG; }
     std::lock_guard<std::mutex> lk(h->mu);
-    auto it = h->relays.find(relay_id);
-    if (it == h->relays.end()) return GA_OK;                 // nonexistent relay: not an error (:916-923, test :316)
-    const uint32_t slot = it->second.slot, shard = it->second.shard;
-    h->relays.erase(it);
+    auto it = h->by_id.find(relay_id);
+    if (it == h->by_id.end()) return GA_OK;                  // nonexistent relay: not an error (:916-923, test :316)
+    Relay &r = h->table[it->second];
+    const uint32_t slot = r.slot, shard = r.shard;
+    // chunks of the relay that were not flushed yet go with it — the slot may get a new owner before
+    // the next tick: the flush drops queued chunks whose generation is not the slot's current one
+    // (their ring space is released with the rest of the flush's prefix)
+    r.gen.store(r.gen.load() + 1, std::memory_order_release);           // odd -> even: free; stale handles are refused
+    r.alive = false;
+    r.in_active_streams.store(false);
+    r.id.clear();
+    h->by_id.erase(it);
     h->free_slots[shard].push_back(slot);
-    // chunks of the relay that were not flushed yet go with it: the slot may get a new owner before
-    // the next tick (their ring space is released with the next ticket that is waited)
-    auto &q = h->pending[shard];
-    q.erase(std::remove_if(q.begin(), q.end(), [slot](const ga_msg &m) { return m.stream_id == slot; }), q.end());
     return h->ctxs.empty() ? GA_OK : ga_stream_reset(h->ctxs[shard], slot);
     GA_GUARD_END
 }
@@ -548,7 +730,7 @@ extern "C" int ga_hub_active_streams(ga_hub *h, uint32_t *n)
     if (!h || !n) { set_error("ga_hub_active_streams: bad argument"); return GA_ERR_ARG; }
     std::lock_guard<std::mutex> lk(h->mu);
     uint32_t c = 0;
-    for (auto &kv : h->relays) c += kv.second.in_active_streams ? 1u : 0u;
+    for (auto &kv : h->by_id) c += h->table[kv.second].in_active_streams.load() ? 1u : 0u;
     *n = c;
     return GA_OK;
     GA_GUARD_END

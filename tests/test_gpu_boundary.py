@@ -106,3 +106,65 @@ def test_arbitrate_reuses_its_scratch_and_handles_growing_window_sets():
                 a, b = seg[w], seg[w + 1]
                 assert winner[w] == a + int(np.argmax(want[a:b]))
             assert (status == L.RELAY_WINNER).sum() == len(seg) - 1
+
+
+def test_wait_view_records_survive_until_the_slot_comes_round_again():
+    """ga_wait_view hands out the slot's pinned buffers; slots are used round-robin, so ticket t's
+    records are overwritten only by the submit that returns ticket t + max_inflight."""
+    with make(max_inflight=3, ring_bytes=1 << 20) as c:
+        def one(n):
+            m = np.zeros(2, dtype=L.MSG_DTYPE)
+            m["ring_offset"] = [c.push(bytes([n]) * 200), c.push(bytes([n + 100]) * 64)]
+            m["nbytes"] = [200, 64]; m["stream_id"] = [n % 64, (n + 1) % 64]
+            return m
+        want = lambda n: (ora.sha256(bytes([n]) * 200), ora.sha256(bytes([n + 100]) * 64))
+        t1, t2 = c.submit(one(1)), c.submit(one(2))
+        view1, _ = c.wait_view(t1)
+        t3 = c.submit(one(3))                      # tickets 2 and 3 live in the other two slots
+        c.wait(t2); c.wait(t3)
+        assert (view1["digest"][0].tobytes(), view1["digest"][1].tobytes()) == want(1)
+        view_ptr = view1.ctypes.data
+        t4 = c.submit(one(4))                      # ticket 4 reuses ticket 1's slot ...
+        view4, _ = c.wait_view(t4)
+        assert view4.ctypes.data == view_ptr       # ... and therefore its buffers
+        assert (view4["digest"][0].tobytes(), view4["digest"][1].tobytes()) == want(4)
+        # in a FULL pipeline the very next submit is the one that comes round
+        ts = [c.submit(one(n)) for n in (5, 6, 7)]
+        v5, _ = c.wait_view(ts[0])
+        assert v5["digest"][0].tobytes() == want(5)[0]
+        t8 = c.submit(one(8))
+        for t in ts[1:] + [t8]:
+            last, _ = c.wait_view(t)
+        assert last.ctypes.data == v5.ctypes.data and last["digest"][0].tobytes() == want(8)[0]
+
+
+def test_a_failed_submit_keeps_the_fence_of_the_streams_it_touched():
+    """A refused batch must restore, not clear, the ticket that last appended to each stream it had
+    already walked over: a restart of such a stream in the next batch still has to wait for the
+    batch in flight that writes the same arena space (tickets run on separate CUDA streams)."""
+    rng = np.random.default_rng(21)
+    S, chunk, T = 32, 6400, 10
+    old = rng.integers(0, 256, size=(T, S, chunk), dtype=np.uint8)
+    new = rng.integers(0, 256, size=(S, chunk), dtype=np.uint8)
+    with make(max_streams=S + 1, max_batch_msgs=T * S, max_inflight=3, ring_bytes=16 << 20, arena_samples=40_000,
+              wake_samples_max=400, mode=L.DO_ALL) as c:
+        for _ in range(4):
+            m1 = np.zeros(T * S, dtype=L.MSG_DTYPE)
+            m1["ring_offset"] = [c.push(old[t, s]) for t in range(T) for s in range(S)]
+            m1["nbytes"] = chunk; m1["stream_id"] = np.tile(np.arange(S), T)
+            m1["flags"][:S] = L.MSG_FIRST
+            t1 = c.submit(m1)                                   # in flight, not waited
+            bad = np.zeros(S + 1, dtype=L.MSG_DTYPE)            # walks over every stream, then fails
+            bad["ring_offset"][:S] = m1["ring_offset"][:S]; bad["nbytes"] = chunk
+            bad["stream_id"] = np.arange(S + 1); bad["stream_id"][S] = 4000
+            with pytest.raises(L.GpuAudioError):
+                c.submit(bad)
+            assert c.stream_info(3) == (T * chunk // 2, 0)
+            m2 = np.zeros(S, dtype=L.MSG_DTYPE)
+            m2["ring_offset"] = [c.push(new[s]) for s in range(S)]
+            m2["nbytes"] = chunk; m2["stream_id"] = np.arange(S); m2["flags"] = L.MSG_FIRST
+            t2 = c.submit(m2)
+            c.wait(t1); c.wait(t2)
+            for sid in (0, 13, S - 1):
+                assert c.stream_info(sid) == (chunk // 2, 0)
+                assert np.array_equal(c.fetch_samples(sid), ora.bytes_to_float32(new[sid].tobytes())[0])

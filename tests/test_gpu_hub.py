@@ -306,3 +306,177 @@ def test_cleanup_drops_the_relays_unflushed_chunks(svc):
     assert svc.flush() == 1
     assert np.array_equal(svc.ctx.fetch_samples(slot), ora.bytes_to_float32(mine)[0])
     svc.ctx.push(b"\0" * 16)                             # the ring keeps working past the skipped reservation
+
+
+def small_hub(**kw):
+    import __graft_entry__ as entry
+    entry.build()
+    args = dict(device=0, max_streams=16, max_batch_msgs=8, max_inflight=2, ring_bytes=1 << 16,
+                arena_samples=4_000, wake_samples_max=1_280, mode=L.DO_ALL)
+    args.update(kw)
+    ctx = api.Context(**args)
+    return ctx, AudioService(ctx, max_streams=args["max_streams"], window_duration_us=100 * MS)
+
+
+def test_flush_cuts_the_queue_at_the_contexts_batch_limit():
+    """More chunks queued than one ga_submit takes (max_batch_msgs = 8): the flush goes through them in
+    several batches instead of failing and re-queueing for ever."""
+    ctx, svc = small_hub()
+    try:
+        rng = np.random.default_rng(1)
+        data = {r: rng.integers(-20000, 20000, size=5 * 320).astype("<i2") for r in range(6)}
+        for r in range(6):
+            svc.connect("r%d" % r, group=r)
+        for m in range(5):
+            for r in range(6):
+                assert svc.on_chunk("r%d" % r, data[r][m * 320:(m + 1) * 320].tobytes(), m < 2, m == 4, m * MS)
+        assert svc.flush() == 30
+        assert svc.flush() == 0
+        for r in range(6):
+            slot = svc.relay("r%d" % r).slot
+            assert ctx.stream_info(slot) == (1600, 640)
+            want, _ = ora.bytes_to_float32(data[r].tobytes())
+            assert np.array_equal(ctx.fetch_samples(slot).view(np.uint32), want.view(np.uint32))
+    finally:
+        svc.close(); ctx.close()
+
+
+def test_a_relay_that_overflows_its_arena_does_not_wedge_the_hub():
+    """The reference appends speech without bound (audio_service.go:1002); a stream slot here has a
+    fixed arena.  The relay that runs over loses the tick's chunks and leaves activeStreams; every
+    other relay's chunks are ingested and later ticks work."""
+    ctx, svc = small_hub(max_batch_msgs=64)
+    try:
+        svc.connect("talker", group=0)
+        svc.connect("other", group=1)
+        chunk = pcm(np.full(320, 1234))
+        mine = [pcm(np.full(320, 100 + m)) for m in range(8)]
+        assert svc.on_chunk("talker", chunk, True, False, 0)
+        assert svc.on_chunk("other", mine[0], True, False, 0)
+        assert svc.flush() == 2
+        for m in range(9):                               # speech arena = 4,000 - 1,280 = 2,720 samples = 8.5 chunks
+            assert svc.on_chunk("talker", chunk, False, False, (m + 1) * MS)
+            if m < 5:
+                assert svc.on_chunk("other", mine[m + 1], False, False, (m + 1) * MS)
+        with pytest.raises(L.GpuAudioError) as e:
+            svc.flush()
+        assert e.value.code == L.GA_ERR_OVERFLOW and "dropped 9" in str(e.value)
+        slot_o, slot_t = svc.relay("other").slot, svc.relay("talker").slot
+        assert ctx.stream_info(slot_o) == (6 * 320, 320)            # everybody else's chunks went in
+        assert ctx.stream_info(slot_t) == (320, 320)
+        assert not svc.is_relay_active("talker")
+        assert svc.flush() == 0                                      # nothing is stuck in the queue
+        for m in range(6):
+            svc.on_chunk("talker", chunk, False, False, (20 + m) * MS)   # not in activeStreams any more: ignored
+            if m < 2:
+                assert svc.on_chunk("other", mine[6 + m], False, False, (20 + m) * MS)
+            assert svc.flush() == (1 if m < 2 else 0)
+        want = np.concatenate([ora.bytes_to_float32(c)[0] for c in mine])
+        assert np.array_equal(ctx.fetch_samples(slot_o).view(np.uint32), want.view(np.uint32))
+    finally:
+        svc.close(); ctx.close()
+
+
+def test_ring_space_of_dropped_chunks_comes_back():
+    """Chunks that never reach a ticket (their relay was cleaned up before the tick) must still give
+    their ring space back, or a hub whose relays come and go fills its pinned ring."""
+    ctx, svc = small_hub(ring_bytes=1 << 14, max_batch_msgs=64, arena_samples=16_000, wake_samples_max=8_000)
+    try:
+        chunk = pcm(np.arange(320))
+        for round_ in range(6):                          # 6 x 20 x 640 B through a 16 KiB ring
+            svc.connect("ghost", group=round_)
+            for m in range(20):
+                assert svc.on_chunk("ghost", chunk, True, False, m * MS)
+            svc.cleanup_relay("ghost")
+            assert svc.flush() == 0                      # all 20 belonged to a relay that is gone
+        svc.connect("real", group=99)
+        for m in range(20):
+            assert svc.on_chunk("real", chunk, True, False, m * MS)
+        assert svc.flush() == 20
+        assert ctx.stream_info(svc.relay("real").slot) == (20 * 320, 20 * 320)
+    finally:
+        svc.close(); ctx.close()
+
+
+def test_chunks_by_handle_and_stale_handles(svc):
+    svc.connect("a", group=3)
+    svc.connect("b", group=3)
+    ha, hb = svc.relay_handle("a"), svc.relay_handle("b")
+    loud, quiet = pcm(np.full(640, 9000)), pcm(np.full(640, 700))
+    assert svc.on_chunk_h(hb, quiet, True, False, 0)
+    assert svc.on_chunk_h(ha, loud, True, False, 1 * MS)
+    svc.on_chunk_h(hb, quiet, False, True, 2 * MS)
+    assert svc.flush() == 3
+    assert svc.poll(200 * MS) == 1
+    assert svc.relay("a").status == RelayStatusWinner and svc.relay("b").status == RelayStatusCancelled
+    assert svc.relay("a").signal_strength == ora.signal_strength(ora.bytes_to_float32(loud)[0])[0]
+    svc.cleanup_relay("b")
+    with pytest.raises(L.GpuAudioError) as e:
+        svc.on_chunk_h(hb, quiet, True, False, 300 * MS)
+    assert e.value.code == L.GA_ERR_STATE
+    svc.connect("c", group=9)                            # inherits b's slot; b's old handle stays dead
+    assert svc.relay("c").slot == 1 and svc.relay_handle("c") != hb
+    with pytest.raises(L.GpuAudioError):
+        svc.on_chunk_h(hb, quiet, True, False, 300 * MS)
+    assert svc.on_chunk_h(svc.relay_handle("c"), quiet, True, False, 300 * MS)
+    assert svc.flush() == 1
+
+
+def test_many_relay_threads_through_handles_while_a_batcher_flushes():
+    """The per-chunk path under load: 8 threads push 20 ms chunks of 256 relays through
+    ga_hub_on_chunk_h while one thread flushes; every stream must end up holding exactly its own
+    utterance (order per relay kept, nothing lost, nothing duplicated)."""
+    import threading
+    import __graft_entry__ as entry
+    entry.build()
+    S, n_msgs, wake, ms, n_thr = 256, 30, 3, 320, 8
+    ctx = api.Context(device=0, max_streams=S, max_batch_msgs=2048, max_inflight=2, ring_bytes=16 << 20,
+                      arena_samples=n_msgs * ms, wake_samples_max=wake * ms, mode=L.DO_ALL)
+    svc = AudioService(ctx, max_streams=S, window_duration_us=10_000 * MS)
+    try:
+        data = ora.synth_fill(40, S, 8, n_msgs, ms)                  # [S][n_msgs][ms]
+        handles = []
+        for s in range(S):
+            svc.connect("r%d" % s, group=s // 8)
+            handles.append(svc.relay_handle("r%d" % s))
+        stop, errors, flushed = threading.Event(), [], [0]
+
+        def relay_thread(mine):
+            try:
+                for m in range(n_msgs):
+                    for s in mine:
+                        while True:
+                            try:
+                                svc.on_chunk_h(handles[s], data[s, m].view(np.uint8), m < wake, m == n_msgs - 1, m * MS)
+                                break
+                            except L.GpuAudioError as e:             # back-pressure: wait for the batcher
+                                if e.code != L.GA_ERR_RING_FULL:
+                                    raise
+            except Exception as e:                                   # noqa: BLE001
+                errors.append(e)
+
+        def batcher():
+            try:
+                while not stop.is_set():
+                    flushed[0] += svc.flush()
+                flushed[0] += svc.flush()
+            except Exception as e:                                   # noqa: BLE001
+                errors.append(e)
+
+        threads = [threading.Thread(target=relay_thread, args=(range(i, S, n_thr),)) for i in range(n_thr)]
+        bt = threading.Thread(target=batcher)
+        bt.start()
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        stop.set()
+        bt.join()
+        assert not errors, errors
+        assert flushed[0] == S * n_msgs
+        for s in range(0, S, 7):
+            want, _ = ora.bytes_to_float32(data[s].tobytes())
+            assert ctx.stream_info(svc.relay("r%d" % s).slot) == (n_msgs * ms, wake * ms)
+            assert np.array_equal(ctx.fetch_samples(svc.relay("r%d" % s).slot).view(np.uint32), want.view(np.uint32)), s
+    finally:
+        svc.close(); ctx.close()
