@@ -98,7 +98,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sweep", action="store_true", help="N = 1: skip the cfg2 / cfg4 / cfg5_shard sweep")
     ap.add_argument("--sweep-steps", type=int, default=5)
-    ap.add_argument("--fill-threads", type=int, default=8, help="host threads of the e2e_with_fill leg")
+    ap.add_argument("--fill-threads", type=int, default=0, help="host threads of the e2e with_fill leg (0 = all)")
     ap.add_argument("--cpu-threads", type=int, default=0)
     args = ap.parse_args()
     if args.workload is None:
@@ -674,9 +674,10 @@ def run_e2e(env, w, plan, pcm, arbitration, d_winner, steps):
     # The ring holds the whole step when that is at most ~1.4 GB; otherwise it holds n_host submits and
     # the step goes round it several times — later submits re-send the bytes of the first n_host (the
     # wake-word part that arbitration reads is in submits 0-1 and is the real data)
-    n_host = n_sub
-    while n_host > 2 and (sub_bytes * n_host > (1400 << 20) or n_sub % n_host):
-        n_host -= 1
+    # (at least 5 submits, so that 4 tickets can be in flight while the next one is reserved)
+    cands = [d for d in range(1, n_sub + 1) if n_sub % d == 0 and (d >= 5 or d == n_sub)]
+    fits = [d for d in cands if sub_bytes * d <= (1700 << 20)]
+    n_host = max(fits) if fits else min(cands)
     ring_bytes = sub_bytes * n_host
     ctx = api.Context(device=env.local_rank, max_streams=S, max_batch_msgs=sub_msgs, max_inflight=4,
                       ring_bytes=ring_bytes, arena_samples=M * ms, wake_samples_max=wake * ms,
@@ -708,7 +709,7 @@ def run_e2e(env, w, plan, pcm, arbitration, d_winner, steps):
     # per-message descriptors (32 B each, 96 B for 48 kHz) or, for ga_submit_ticks, 1 flag byte per message + 20 B per stream
     h2d = sub_bytes * n_sub + (n_sub * (sub_msgs + 20 * S) if ticks else sub_msgs * n_sub * (96 if fmt48 else 32))
     d2h = sub_msgs * n_sub * 64 + plan.n_windows * 4
-    nfill = max(1, args.fill_threads)
+    nfill = max(1, args.fill_threads or host_threads(args))
     pool = ThreadPoolExecutor(nfill)
     cuts = [sub_bytes * i // nfill // 64 * 64 for i in range(nfill)] + [sub_bytes]
 

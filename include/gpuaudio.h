@@ -424,6 +424,22 @@ int ga_arbitrate(ga_ctx *ctx, const uint32_t *seg_offsets, uint32_t n_windows,
 int ga_fetch_wav(ga_ctx *ctx, uint32_t stream_id, uint32_t sample_rate, uint8_t *out, size_t cap,
                  size_t *n_bytes);
 
+/* The winner path for MANY streams in one call — what runs once per closed window in the reference:
+ * processWinningRelayAudio (audio_service.go:590-609, fullAudio = WakeWordSignal ++ SpeechAudio),
+ * float32ToWAV (internal/llm/stt_client.go:365-398) and the fingerprint of those samples
+ * (events/voice_event.go:84-88).  One gather launch packs the n WAV files, one chained SHA-256
+ * launch hashes the samples where they lie, ONE device->host copy brings all of it into C-owned
+ * pinned memory; no allocation per call (the staging grows on demand and is kept), and the
+ * context is locked only while the work is queued, so ga_submit is not held up.
+ *   *wavs + offsets[k]  = WAV file of stream_ids[k] (44 + 4 * n_samples bytes; offsets[n] ends the
+ *                         last one; files are padded apart), valid until the next ga_fetch_wavs /
+ *                         ga_samples_digest(s) call on this context;
+ *   digests (nullable)  = 32 bytes per stream: SHA-256 of the samples' little-endian f32 bytes. */
+int ga_fetch_wavs(ga_ctx *ctx, const uint32_t *stream_ids, uint32_t n, uint32_t sample_rate,
+                  const uint8_t **wavs, uint64_t *offsets, uint8_t *digests);
+/* ga_samples_digest for n streams in one launch. */
+int ga_samples_digests(ga_ctx *ctx, const uint32_t *stream_ids, uint32_t n, uint8_t *digests);
+
 /* ===================================================================== hub (window manager)
  * Host-side mirror of the reference's AudioService for this path (internal/grpc/audio_service.go):
  * relay registry, arbitration-window lifecycle, per-chunk routing.  It is the logic the Go code
@@ -471,6 +487,14 @@ int  ga_hub_perform_arbitration(ga_hub *hub, uint64_t window_id);
 /* … and runArbitrationTimer :494-502 for all groups: every active window whose duration has
  * elapsed at now_us is arbitrated in ONE ga_arbitrate call. */
 int  ga_hub_poll(ga_hub *hub, uint64_t now_us, uint32_t *n_closed);
+/* ga_hub_poll that also reports which windows it closed (at most cap ids; *n_closed = all). */
+int  ga_hub_poll_windows(ga_hub *hub, uint64_t now_us, uint64_t *window_ids, uint32_t cap, uint32_t *n_closed);
+/* processWinningRelayAudio (:590-609) for the winners of n closed windows at once: per GPU one
+ * ga_fetch_wavs.  wav_ptrs[k] / wav_bytes[k] = the winner's WAV file for the STT request, inside
+ * C-owned pinned memory (valid until the next call); audio_hashes (nullable, GA_AUDIO_HASH_LEN
+ * bytes per window) = "sha256:<hex>" of its samples.  No winner: NULL / 0 / "". */
+int  ga_hub_fetch_winner_wavs(ga_hub *hub, const uint64_t *window_ids, uint32_t n, uint32_t sample_rate,
+                              const uint8_t **wav_ptrs, uint64_t *wav_bytes, char *audio_hashes);
 int  ga_hub_window_info(ga_hub *hub, uint64_t window_id, int *is_active, char *winner_id,
                         size_t winner_cap, uint32_t *n_relays);
 int  ga_hub_active_window(ga_hub *hub, uint32_t group, uint64_t *window_id);   /* 0 = nil */

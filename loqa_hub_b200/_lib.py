@@ -110,6 +110,10 @@ SYMBOLS = {
     "ga_hub_start_window": (_i32, [_vp, C.c_char_p, _u64, C.POINTER(_u64)]),
     "ga_hub_join_window": (_i32, [_vp, C.c_char_p, _u64, C.POINTER(_i32)]),
     "ga_hub_on_chunk": (_i32, [_vp, C.c_char_p, _vp, _u32, _i32, _i32, _u64, C.POINTER(_i32)]),
+    "ga_fetch_wavs": (_i32, [_vp, _vp, _u32, _u32, C.POINTER(_vp), _vp, _vp]),
+    "ga_samples_digests": (_i32, [_vp, _vp, _u32, _vp]),
+    "ga_hub_poll_windows": (_i32, [_vp, _u64, _vp, _u32, C.POINTER(_u32)]),
+    "ga_hub_fetch_winner_wavs": (_i32, [_vp, _vp, _u32, _u32, _vp, _vp, _vp]),
     "ga_hub_relay_handle": (_i32, [_vp, C.c_char_p, C.POINTER(_u64)]),
     "ga_hub_on_chunk_h": (_i32, [_vp, _u64, _vp, _u32, _i32, _i32, _u64, C.POINTER(_i32)]),
     "ga_hub_flush": (_i32, [_vp, C.POINTER(_u32)]),

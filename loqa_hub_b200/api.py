@@ -247,6 +247,27 @@ class Context:
         check(load().ga_samples_digest(self._h, stream_id, ptr(out)))
         return out.tobytes()
 
+    def samples_digests(self, stream_ids):
+        ids = np.ascontiguousarray(stream_ids, dtype=np.uint32)
+        out = np.zeros((ids.size, 32), dtype=np.uint8)
+        check(load().ga_samples_digests(self._h, ptr(ids), ids.size, ptr(out)))
+        return [out[i].tobytes() for i in range(ids.size)]
+
+    def fetch_wavs(self, stream_ids, sample_rate=16000, digests=True):
+        """ga_fetch_wavs: (list of WAV byte strings, list of 32-byte digests or None) for many streams."""
+        ids = np.ascontiguousarray(stream_ids, dtype=np.uint32)
+        base = C.c_void_p()
+        off = np.zeros(ids.size + 1, dtype=np.uint64)
+        dg = np.zeros((ids.size, 32), dtype=np.uint8) if digests else None
+        check(load().ga_fetch_wavs(self._h, ptr(ids), ids.size, sample_rate, C.byref(base), off.ctypes.data_as(C.c_void_p),
+                                   ptr(dg) if digests else None))
+        wavs = []
+        for k in range(ids.size):
+            hdr = C.string_at(base.value + int(off[k]), 8)
+            size = 8 + int.from_bytes(hdr[4:8], "little")
+            wavs.append(C.string_at(base.value + int(off[k]), size))
+        return wavs, ([dg[i].tobytes() for i in range(ids.size)] if digests else None)
+
     def stream_reset(self, stream_id):
         check(load().ga_stream_reset(self._h, stream_id))
 

@@ -108,6 +108,27 @@ class AudioService:
         L.check(L.load().ga_hub_poll(self._h, now_us, C.byref(n)))
         return n.value
 
+    def poll_windows(self, now_us, cap=65536):
+        """ga_hub_poll_windows: ids of the windows this poll closed."""
+        ids = np.zeros(cap, dtype=np.uint64)
+        n = C.c_uint32()
+        L.check(L.load().ga_hub_poll_windows(self._h, now_us, L.ptr(ids), cap, C.byref(n)))
+        return [int(x) for x in ids[:min(n.value, cap)]]
+
+    def fetch_winner_wavs(self, window_ids, sample_rate=16000, hashes=True):
+        """ga_hub_fetch_winner_wavs: [(wav bytes | None, "sha256:<hex>" | "")] per window."""
+        ids = np.ascontiguousarray(window_ids, dtype=np.uint64)
+        n = ids.size
+        ptrs = (C.c_void_p * max(n, 1))()
+        sizes = np.zeros(max(n, 1), dtype=np.uint64)
+        hs = C.create_string_buffer(72 * max(n, 1)) if hashes else None
+        L.check(L.load().ga_hub_fetch_winner_wavs(self._h, L.ptr(ids), n, sample_rate, ptrs, L.ptr(sizes), hs))
+        out = []
+        for k in range(n):
+            wav = C.string_at(ptrs[k], int(sizes[k])) if ptrs[k] else None
+            out.append((wav, hs.raw[72 * k:72 * (k + 1)].split(b"\0")[0].decode() if hashes else ""))
+        return out
+
     def window(self, window_id):
         a, n = C.c_int(), C.c_uint32()
         buf = C.create_string_buffer(256)

@@ -97,6 +97,16 @@ struct ga_ctx {
     std::mutex mu;   // guards submit/wait/arbitrate bookkeeping (not the ring reserve path)
     // scratch for ga_arbitrate
     cudaStream_t aux = nullptr;
+    // Readers of the sample arena on `aux` (arbitration, the winner path) queue their work under `mu`
+    // and wait for it WITHOUT `mu`, so the batching thread's ga_submit is never held up by a window
+    // close.  A later submit that restarts a stream must not overwrite samples such a reader is still
+    // reading: its CUDA stream waits for aux_ev (recorded behind the reader's work).
+    cudaEvent_t aux_ev = nullptr;
+    bool aux_used = false;
+    std::mutex arb_mu;      // one ga_arbitrate at a time (they share d_arb / h_arb)
+    std::mutex win_mu;      // one winner-path call at a time (they share d_win / h_win)
+    uint8_t *d_win = nullptr, *h_win = nullptr;   // grow-only staging of ga_fetch_wavs / ga_samples_digests
+    size_t win_bytes = 0;
 };
 
 namespace ga {
@@ -130,6 +140,9 @@ static void destroy(ga_ctx *c)
         if (s.stream) cudaStreamDestroy(s.stream);
     }
     if (c->aux) cudaStreamDestroy(c->aux);
+    if (c->aux_ev) cudaEventDestroy(c->aux_ev);
+    if (c->d_win) cudaFree(c->d_win);
+    if (c->h_win) cudaFreeHost(c->h_win);
     if (c->h_ring) cudaFreeHost(c->h_ring);
     if (c->d_ring) cudaFree(c->d_ring);
     if (c->d_arena) cudaFree(c->d_arena);
@@ -279,6 +292,7 @@ extern "C" int ga_init(const ga_config *cfg, ga_ctx **out)
         catch (...) { set_error("ga_init: out of host memory"); destroy(c); return GA_ERR_NOMEM; }
     }
     GA_ALLOC_TRY(cudaStreamCreateWithFlags(&c->aux, cudaStreamNonBlocking));
+    GA_ALLOC_TRY(cudaEventCreateWithFlags(&c->aux_ev, cudaEventDisableTiming));
     if ((cfg->mode & GA_DO_CONVERT) && arb_reserve(c, 26ull * cfg->max_streams + 4096) != GA_OK) { destroy(c); return GA_ERR_NOMEM; }
     *out = c;
     return GA_OK;
@@ -319,6 +333,8 @@ extern "C" int ga_ring_reserve(ga_ctx *ctx, uint64_t nbytes, void **host_ptr, ui
 // may still be writing the arena space the new utterance starts over in: order the two.
 static int fence_wait(ga_ctx *ctx, cudaStream_t s, uint64_t fence)
 {
+    // arena readers on the aux stream that were queued before this batch (see ga_ctx::aux_ev)
+    if (ctx->aux_used) GA_CUDA_TRY(cudaStreamWaitEvent(s, ctx->aux_ev, 0));
     if (fence < ctx->oldest_ticket) return GA_OK;
     for (auto &o : ctx->slots)
         if (o.busy && o.ticket <= fence) GA_CUDA_TRY(cudaStreamWaitEvent(s, o.done, 0));
@@ -1013,40 +1029,12 @@ extern "C" int ga_device_arena(ga_ctx *ctx, void **d_arena)
     return GA_OK;
 }
 
+extern "C" int ga_samples_digests(ga_ctx *ctx, const uint32_t *stream_ids, uint32_t n, uint8_t *digests);
 extern "C" int ga_samples_digest(ga_ctx *ctx, uint32_t stream_id, uint8_t digest[32])
 {
     if (!ctx || !digest || stream_id >= ctx->cfg.max_streams) { set_error("ga_samples_digest: bad argument"); return GA_ERR_ARG; }
     if (!ctx->d_arena) { set_error("ga_samples_digest: context does not materialise samples"); return GA_ERR_STATE; }
-    std::lock_guard<std::mutex> lk(ctx->mu);
-    int rc = set_device(ctx);
-    if (rc) return rc;
-    const StreamState st = ctx->streams[stream_id];
-    if ((st.wake_n | st.speech_n) >> 30) { set_error("ga_samples_digest: stream too long for one chained hash"); return GA_ERR_ARG; }
-    // the two arena regions are hashed as two chained "messages" of one running SHA-256
-    struct Pack { ga_sha_state state; ga_desc desc[2]; uint32_t next[2]; uint32_t first[2]; uint8_t out[32]; };
-    static_assert(offsetof(Pack, desc) % 16 == 0, "descriptor alignment");
-    Pack h;
-    std::memset(&h, 0, sizeof h);
-    const uint64_t base = static_cast<uint64_t>(stream_id) * ctx->cfg.arena_samples * 4;
-    h.desc[0].in_off = base;                                   h.desc[0].nbytes = static_cast<uint32_t>(st.wake_n * 4);
-    h.desc[1].in_off = base + ctx->cfg.wake_samples_max * 4;   h.desc[1].nbytes = static_cast<uint32_t>(st.speech_n * 4);
-    h.desc[0].flags = GA_MSG_FIRST;                            // (re)starts the running hash
-    h.next[0] = 1; h.next[1] = 0xffffffffu; h.first[0] = 0;
-    uint8_t *d = nullptr;
-    GA_CUDA_TRY(cudaMalloc(reinterpret_cast<void **>(&d), sizeof(Pack)));
-    cudaStream_t s = ctx->aux;
-    cudaError_t e = cudaSuccess;
-    rc = join_inflight(ctx, s);
-    if (!rc) e = cudaMemcpyAsync(d, &h, sizeof h, cudaMemcpyHostToDevice, s);
-    Pack *dp = reinterpret_cast<Pack *>(d);
-    if (!rc && e == cudaSuccess) rc = ga_k_sha256_chain(ctx->d_arena, dp->desc, dp->first, dp->next, 1, &dp->state, s);
-    if (!rc && e == cudaSuccess) rc = ga_k_sha256_final(&dp->state, nullptr, 1, dp->out, nullptr, s);
-    if (!rc && e == cudaSuccess) e = cudaMemcpyAsync(digest, dp->out, 32, cudaMemcpyDeviceToHost, s);
-    if (!rc && e == cudaSuccess) e = cudaStreamSynchronize(s);
-    cudaFree(d);
-    if (rc) return rc;
-    if (e != cudaSuccess) { set_error("ga_samples_digest: %s", cudaGetErrorString(e)); return GA_ERR_CUDA; }
-    return GA_OK;
+    return ga_samples_digests(ctx, &stream_id, 1, digest);      // the batched path: no allocation, lock dropped before the wait
 }
 
 extern "C" int ga_fetch_samples(ga_ctx *ctx, uint32_t stream_id, uint64_t first, uint64_t n, float *out)
@@ -1074,6 +1062,173 @@ extern "C" int ga_fetch_samples(ga_ctx *ctx, uint32_t stream_id, uint64_t first,
     }
     GA_CUDA_TRY(cudaStreamSynchronize(ctx->aux));
     return GA_OK;
+}
+
+
+// ---------------------------------------------------------------- the winner path, batched
+// What runs once per closed window in the reference — processWinningRelayAudio
+// (audio_service.go:590-609: fullAudio = WakeWordSignal ++ SpeechAudio), float32ToWAV
+// (internal/llm/stt_client.go:365-398) and the voice-event fingerprint of those samples
+// (events/voice_event.go:84-88) — for MANY winners in one call: one gather launch packs every
+// winner's WAV file into a staging buffer, one chained SHA-256 launch hashes their f32 bytes in
+// place in the arena, ONE device->host copy brings everything into C-owned pinned memory.  The
+// context lock is held only while the work is queued.
+namespace ga {
+
+struct WavItem {            // one winner, 48 bytes
+    uint64_t wake_src;      // index of the stream's first wake-word sample in the arena
+    uint64_t speech_src;    // index of its first speech sample
+    uint64_t dst;           // byte offset of the WAV file in the staging buffer (== 4 mod 16: data 16-byte aligned)
+    uint32_t wake_n, speech_n;
+    uint32_t sample_rate, pad;
+};
+
+constexpr int kWavBlocksPerItem = 8;
+
+__global__ void __launch_bounds__(256)
+wav_pack_kernel(const float *__restrict__ arena, const WavItem *items, uint8_t *out)   // items and out share the staging buffer
+{
+    const WavItem it = items[blockIdx.x / kWavBlocksPerItem];
+    const uint32_t part = blockIdx.x % kWavBlocksPerItem;
+    const uint32_t n = it.wake_n + it.speech_n, data_size = n * 4u;
+    uint32_t *hdr = reinterpret_cast<uint32_t *>(out + it.dst);
+    if (part == 0 && threadIdx.x < 11) {
+        // stt_client.go:375-388, as eleven little-endian words
+        const uint32_t w[11] = {0x46464952u /* RIFF */, 36u + data_size, 0x45564157u /* WAVE */, 0x20746d66u /* "fmt " */,
+                                16u, 3u | (1u << 16) /* IEEE float, mono */, it.sample_rate, it.sample_rate * 4u,
+                                4u | (32u << 16) /* block align, bits */, 0x61746164u /* data */, data_size};
+        hdr[threadIdx.x] = w[threadIdx.x];
+    }
+    float *dst = reinterpret_cast<float *>(out + it.dst + 44);
+    const float *wk = arena + it.wake_src, *sp = arena + it.speech_src;
+    for (uint32_t i = part * blockDim.x + threadIdx.x; i < n; i += kWavBlocksPerItem * blockDim.x)
+        dst[i] = i < it.wake_n ? wk[i] : sp[i - it.wake_n];       // :592-594 order, :391-396 payload
+}
+
+static int win_reserve(ga_ctx *ctx, size_t need)
+{
+    if (need <= ctx->win_bytes) return GA_OK;
+    GA_CUDA_TRY(cudaStreamSynchronize(ctx->aux));
+    if (ctx->d_win) cudaFree(ctx->d_win);
+    if (ctx->h_win) cudaFreeHost(ctx->h_win);
+    ctx->d_win = nullptr; ctx->h_win = nullptr; ctx->win_bytes = 0;
+    const size_t want = need + need / 2;
+    cudaError_t e = cudaMalloc(reinterpret_cast<void **>(&ctx->d_win), want);
+    if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void **>(&ctx->h_win), want, cudaHostAllocDefault);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        if (ctx->d_win) { cudaFree(ctx->d_win); ctx->d_win = nullptr; }
+        set_error("winner staging: allocating %zu bytes failed: %s", want, cudaGetErrorString(e));
+        return GA_ERR_NOMEM;
+    }
+    ctx->win_bytes = want;
+    return GA_OK;
+}
+
+// wavs / digests for n streams.  Outputs point into the pinned staging buffer (valid until the next
+// winner-path call on this context).
+static int winners_impl(ga_ctx *ctx, const uint32_t *stream_ids, uint32_t n, bool want_wav, uint32_t sample_rate,
+                        bool want_digest, const uint8_t **base, uint64_t *wav_off, const uint8_t **digests)
+{
+    if (!(ctx->cfg.mode & GA_DO_CONVERT)) { set_error("winner path: context does not materialise samples"); return GA_ERR_STATE; }
+    std::lock_guard<std::mutex> wlk(ctx->win_mu);
+    std::unique_lock<std::mutex> lk(ctx->mu);
+    int rc = set_device(ctx);
+    if (rc) return rc;
+    auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
+    // staging layout: items | descs (2 per winner) | next (2) | first (1) || states | digests | wav files
+    const size_t o_item = 0, o_desc = o_item + up(sizeof(WavItem) * n), o_next = o_desc + up(sizeof(ga_desc) * 2 * n),
+                 o_first = o_next + up(8ull * n), o_state = o_first + up(4ull * n), o_dig = o_state + up(sizeof(ga_sha_state) * n),
+                 o_wav = o_dig + up(32ull * n);
+    size_t wav_total = 0;
+    for (uint32_t k = 0; k < n; k++) {
+        if (stream_ids[k] >= ctx->cfg.max_streams) { set_error("winner path: stream_id %u out of range", stream_ids[k]); return GA_ERR_ARG; }
+        const StreamState &st = ctx->streams[stream_ids[k]];
+        if ((st.wake_n + st.speech_n) >> 30) { set_error("winner path: stream %u is too long", stream_ids[k]); return GA_ERR_ARG; }
+        if (want_wav) wav_total += ((44 + 4 * (st.wake_n + st.speech_n) + 15) & ~size_t(15)) + 16;
+    }
+    rc = win_reserve(ctx, o_wav + wav_total + 256);
+    if (rc) return rc;
+    uint8_t *hb = ctx->h_win, *db = ctx->d_win;
+    WavItem *items = reinterpret_cast<WavItem *>(hb + o_item);
+    ga_desc *descs = reinterpret_cast<ga_desc *>(hb + o_desc);
+    uint32_t *next = reinterpret_cast<uint32_t *>(hb + o_next), *first = reinterpret_cast<uint32_t *>(hb + o_first);
+    size_t cur = o_wav;
+    for (uint32_t k = 0; k < n; k++) {
+        const StreamState &st = ctx->streams[stream_ids[k]];
+        const uint64_t base_idx = static_cast<uint64_t>(stream_ids[k]) * ctx->cfg.arena_samples;
+        WavItem &it = items[k];
+        it.wake_src = base_idx; it.speech_src = base_idx + ctx->cfg.wake_samples_max;
+        it.wake_n = static_cast<uint32_t>(st.wake_n); it.speech_n = static_cast<uint32_t>(st.speech_n);
+        it.sample_rate = sample_rate; it.pad = 0;
+        it.dst = cur + 4;                                     // header at == 4 (mod 16): the samples start 16-byte aligned
+        if (want_wav) {
+            if (wav_off) wav_off[k] = it.dst;
+            cur += ((44 + 4 * (st.wake_n + st.speech_n) + 15) & ~size_t(15)) + 16;
+        }
+        // the two arena regions as two chained "messages" of one running SHA-256 (stt_client.go:390-395 byte order)
+        ga_desc &d0 = descs[2 * k], &d1 = descs[2 * k + 1];
+        std::memset(&d0, 0, 2 * sizeof(ga_desc));
+        d0.in_off = base_idx * 4; d0.nbytes = static_cast<uint32_t>(st.wake_n * 4); d0.stream_id = k; d0.flags = GA_MSG_FIRST;
+        d1.in_off = (base_idx + ctx->cfg.wake_samples_max) * 4; d1.nbytes = static_cast<uint32_t>(st.speech_n * 4); d1.stream_id = k;
+        next[2 * k] = 2 * k + 1; next[2 * k + 1] = 0xffffffffu; first[k] = 2 * k;
+    }
+    if (want_wav && wav_off) wav_off[n] = cur + 4;
+    cudaStream_t s = ctx->aux;
+    rc = join_inflight(ctx, s);
+    if (rc) return rc;
+    GA_CUDA_TRY(cudaMemcpyAsync(db, hb, o_state, cudaMemcpyHostToDevice, s));
+    if (want_digest) {
+        rc = ga_k_sha256_chain(ctx->d_arena, reinterpret_cast<ga_desc *>(db + o_desc), reinterpret_cast<uint32_t *>(db + o_first),
+                               reinterpret_cast<uint32_t *>(db + o_next), n, reinterpret_cast<ga_sha_state *>(db + o_state), s);
+        if (rc) return rc;
+        rc = ga_k_sha256_final(reinterpret_cast<ga_sha_state *>(db + o_state), nullptr, n, db + o_dig, nullptr, s);
+        if (rc) return rc;
+    }
+    if (want_wav) {
+        wav_pack_kernel<<<n * kWavBlocksPerItem, 256, 0, s>>>(ctx->d_arena, reinterpret_cast<WavItem *>(db + o_item), db);
+        GA_CHECK_LAUNCH("wav_pack_kernel");
+    }
+    const size_t lo = want_digest ? o_dig : o_wav, hi = want_wav ? cur : o_wav;
+    if (hi > lo) GA_CUDA_TRY(cudaMemcpyAsync(hb + lo, db + lo, hi - lo, cudaMemcpyDeviceToHost, s));
+    GA_CUDA_TRY(cudaEventRecord(ctx->aux_ev, s));
+    ctx->aux_used = true;
+    lk.unlock();                                              // ga_submit goes on meanwhile
+    GA_CUDA_TRY(cudaEventSynchronize(ctx->aux_ev));
+    if (base) *base = hb;
+    if (digests) *digests = hb + o_dig;
+    return GA_OK;
+}
+
+}  // namespace ga
+
+extern "C" int ga_fetch_wavs(ga_ctx *ctx, const uint32_t *stream_ids, uint32_t n, uint32_t sample_rate,
+                             const uint8_t **wavs, uint64_t *offsets, uint8_t *digests)
+{
+    GA_GUARD_BEGIN
+    if (!ctx || !wavs || !offsets || (n && !stream_ids)) { set_error("ga_fetch_wavs: NULL argument"); return GA_ERR_ARG; }
+    *wavs = nullptr;
+    offsets[0] = 0;
+    if (n == 0) return GA_OK;
+    const uint8_t *dg = nullptr;
+    int rc = ga::winners_impl(ctx, stream_ids, n, true, sample_rate, digests != nullptr, wavs, offsets, &dg);
+    if (rc) return rc;
+    if (digests) std::memcpy(digests, dg, 32ull * n);
+    return GA_OK;
+    GA_GUARD_END
+}
+
+extern "C" int ga_samples_digests(ga_ctx *ctx, const uint32_t *stream_ids, uint32_t n, uint8_t *digests)
+{
+    GA_GUARD_BEGIN
+    if (!ctx || (n && (!stream_ids || !digests))) { set_error("ga_samples_digests: NULL argument"); return GA_ERR_ARG; }
+    if (n == 0) return GA_OK;
+    const uint8_t *dg = nullptr;
+    int rc = ga::winners_impl(ctx, stream_ids, n, false, 0, true, nullptr, nullptr, &dg);
+    if (rc) return rc;
+    std::memcpy(digests, dg, 32ull * n);
+    return GA_OK;
+    GA_GUARD_END
 }
 
 // ---------------------------------------------------------------- arbitration (host arrays)
@@ -1126,7 +1281,8 @@ extern "C" int ga_arbitrate(ga_ctx *ctx, const uint32_t *seg_offsets, uint32_t n
     if (!(ctx->cfg.mode & GA_DO_CONVERT)) { set_error("ga_arbitrate: context does not materialise samples"); return GA_ERR_STATE; }
     for (uint32_t w = 0; w < n_windows; w++)
         if (seg_offsets[w] > seg_offsets[w + 1]) { set_error("ga_arbitrate: seg_offsets not monotone at %u", w); return GA_ERR_ARG; }
-    std::lock_guard<std::mutex> lk(ctx->mu);
+    std::lock_guard<std::mutex> alk(ctx->arb_mu);      // the tables are shared; held to the end
+    std::unique_lock<std::mutex> lk(ctx->mu);          // stream cursors + queueing; dropped before the wait
     int rc = set_device(ctx);
     if (rc) return rc;
     // device arrays carved from one grow-only scratch allocation owned by the context, filled
@@ -1164,7 +1320,10 @@ extern "C" int ga_arbitrate(ga_ctx *ctx, const uint32_t *seg_offsets, uint32_t n
     rc = ga_k_arbitrate(ctx->d_arena, d_off, d_cnt, d_st, d_seg, n_windows, n_members, d_sc, d_win, d_so, s);
     if (rc) return rc;
     GA_CUDA_TRY(cudaMemcpyAsync(hb + o_sc, b + o_sc, end - o_sc, cudaMemcpyDeviceToHost, s));
-    GA_CUDA_TRY(cudaStreamSynchronize(s));
+    GA_CUDA_TRY(cudaEventRecord(ctx->aux_ev, s));
+    ctx->aux_used = true;
+    lk.unlock();                                       // ga_submit may go on while the GPU arbitrates
+    GA_CUDA_TRY(cudaEventSynchronize(ctx->aux_ev));
     if (n_members) {
         std::memcpy(scores, hb + o_sc, 8ull * n_members);
         std::memcpy(status_out, hb + o_so, n_members);

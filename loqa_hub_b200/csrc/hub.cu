@@ -611,6 +611,70 @@ extern "C" int ga_hub_poll(ga_hub *h, uint64_t now_us, uint32_t *n_closed)
     GA_GUARD_END
 }
 
+// The same, also telling WHICH windows were closed, so that the caller can fetch all their winners
+// at once (ga_hub_fetch_winner_wavs).  At most cap ids are written; *n_closed is the full count.
+extern "C" int ga_hub_poll_windows(ga_hub *h, uint64_t now_us, uint64_t *window_ids, uint32_t cap, uint32_t *n_closed)
+{
+    GA_GUARD_BEGIN
+    if (!h || (cap && !window_ids)) { set_error("ga_hub_poll_windows: bad argument"); return GA_ERR_ARG; }
+    std::lock_guard<std::mutex> lk(h->mu);
+    std::vector<uint64_t> due;
+    for (auto &kv : h->windows)
+        if (kv.second.is_active && now_us - kv.second.start_us >= kv.second.duration_us) due.push_back(kv.first);
+    if (n_closed) *n_closed = static_cast<uint32_t>(due.size());
+    for (size_t k = 0; k < due.size() && k < cap; k++) window_ids[k] = due[k];
+    return arbitrate_windows(h, due);
+    GA_GUARD_END
+}
+
+// processWinningRelayAudio (:590-609) for the winners of many windows in one go: per GPU one
+// ga_fetch_wavs — every winner's WakeWordSignal ++ SpeechAudio as the WAV file the STT request
+// carries (stt_client.go:365-398) plus, if audio_hashes is given, the voice-event fingerprint
+// "sha256:<hex>" of those samples (events/voice_event.go:84-88; GA_AUDIO_HASH_LEN bytes each).
+// wav_ptrs[k] / wav_bytes[k] describe window k's file inside C-owned pinned memory (valid until the
+// next call); a window without a winner gets NULL / 0 / "".
+extern "C" int ga_hub_fetch_winner_wavs(ga_hub *h, const uint64_t *window_ids, uint32_t n, uint32_t sample_rate,
+                                        const uint8_t **wav_ptrs, uint64_t *wav_bytes, char *audio_hashes)
+{
+    GA_GUARD_BEGIN
+    if (!h || (n && (!window_ids || !wav_ptrs || !wav_bytes))) { set_error("ga_hub_fetch_winner_wavs: bad argument"); return GA_ERR_ARG; }
+    if (h->ctxs.empty()) { set_error("ga_hub_fetch_winner_wavs: this hub has no GPU context"); return GA_ERR_STATE; }
+    std::vector<std::vector<uint32_t>> slots(h->n_shards), which(h->n_shards);
+    {
+        std::lock_guard<std::mutex> lk(h->mu);
+        for (uint32_t k = 0; k < n; k++) {
+            wav_ptrs[k] = nullptr; wav_bytes[k] = 0;
+            if (audio_hashes) audio_hashes[static_cast<size_t>(k) * GA_AUDIO_HASH_LEN] = 0;
+            auto it = h->windows.find(window_ids[k]);
+            if (it == h->windows.end()) { set_error("ga_hub_fetch_winner_wavs: unknown window %llu", (unsigned long long)window_ids[k]); return GA_ERR_STATE; }
+            if (it->second.winner.empty()) continue;
+            Relay *r = find_relay(h, it->second.winner.c_str());
+            if (!r) continue;                                     // the winner was cleaned up meanwhile
+            slots[r->shard].push_back(r->slot);
+            which[r->shard].push_back(k);
+        }
+    }
+    for (uint32_t sh = 0; sh < h->n_shards; sh++) {
+        const uint32_t m = static_cast<uint32_t>(slots[sh].size());
+        if (!m) continue;
+        std::vector<uint64_t> off(m + 1);
+        std::vector<uint8_t> dg(audio_hashes ? 32ull * m : 0);
+        const uint8_t *base = nullptr;
+        int rc = ga_fetch_wavs(h->ctxs[sh], slots[sh].data(), m, sample_rate, &base, off.data(), audio_hashes ? dg.data() : nullptr);
+        if (rc) return rc;
+        for (uint32_t j = 0; j < m; j++) {
+            const uint32_t k = which[sh][j];
+            wav_ptrs[k] = base + off[j];
+            const uint8_t *hdr = base + off[j];
+            wav_bytes[k] = 8ull + (static_cast<uint64_t>(hdr[4]) | (static_cast<uint64_t>(hdr[5]) << 8) |
+                                   (static_cast<uint64_t>(hdr[6]) << 16) | (static_cast<uint64_t>(hdr[7]) << 24));   // RIFF size + 8
+            if (audio_hashes) ga_format_audio_hash(dg.data() + 32ull * j, audio_hashes + static_cast<size_t>(k) * GA_AUDIO_HASH_LEN);
+        }
+    }
+    return GA_OK;
+    GA_GUARD_END
+}
+
 extern "C" int ga_hub_window_info(ga_hub *h, uint64_t window_id, int *is_active, char *winner_id, size_t winner_cap,
                                   uint32_t *n_relays)
 {

@@ -160,7 +160,9 @@ extern "C" int ga_k_sha256_chain(const void *d_pcm, const ga_desc *d_desc, const
     using namespace ga;
     if (n_runs == 0) return GA_OK;
     if (!d_pcm || !d_desc || !d_run_first || !d_next || !d_state) { set_error("ga_k_sha256_chain: NULL argument"); return GA_ERR_ARG; }
-    sha256_chain_kernel<<<(n_runs + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+    // a run is serial; few runs (the winners of a window close) are spread one warp per block over the SMs
+    const uint32_t tpb = n_runs > 128u * 148u ? 128u : 32u;
+    sha256_chain_kernel<<<(n_runs + tpb - 1) / tpb, tpb, 0, static_cast<cudaStream_t>(stream)>>>(
         static_cast<const uint8_t *>(d_pcm), d_desc, d_run_first, d_next, n_runs, d_state);
     GA_CHECK_LAUNCH("sha256_chain_kernel");
     return GA_OK;

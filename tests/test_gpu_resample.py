@@ -155,7 +155,7 @@ def test_saved_history_is_not_overwritten_while_an_earlier_chunk_still_needs_it(
     # come back (their saving chunk) in groups 1-3
     front = [s for s in range(32) if s != 7]
     order = front + [7, 7] + front + list(range(32, 40)) + front[::2]
-    assert len(front) == 31 and order[31] == 7 and order[32] == 7 and 7 not in front and len(order) > 96
+    assert len(front) == 31 and order[31] == 7 and order[32] == 7 and 7 not in front and len(order) > 64
     run(order)
     # batch 3: every stream again, first chunks spread over two groups, second chunks behind them
     run(list(range(n_streams)) + list(range(n_streams - 1, -1, -1)))
