@@ -30,6 +30,7 @@
 #include <memory>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <unordered_map>
 #include <unordered_set>
 #include <vector>
@@ -75,8 +76,28 @@ struct QEntry {
 };
 
 // Chunks pushed since the last flush, per GPU: bounded multi-producer / single-consumer queue.
+// Held for a ring reservation plus one increment (tens of nanoseconds) by every relay thread of a
+// GPU: a spin lock — a futex-based mutex puts contending threads to sleep for longer than that.
+struct SpinLock {
+    std::atomic<bool> held{false};
+    void lock()
+    {
+        for (int spins = 0;; spins++) {
+            if (!held.load(std::memory_order_relaxed) && !held.exchange(true, std::memory_order_acquire)) return;
+            if (spins < 256) {
+#if defined(__x86_64__)
+                __builtin_ia32_pause();
+#endif
+            } else {
+                std::this_thread::yield();
+            }
+        }
+    }
+    void unlock() { held.store(false, std::memory_order_release); }
+};
+
 struct ShardQueue {
-    std::mutex claim;                // held for {ring reservation, sequence number} only
+    SpinLock claim;                  // held for {ring reservation, sequence number} only
     uint64_t tail = 0;               // next sequence number (under claim)
     std::atomic<uint64_t> head{0};   // first sequence number the flush has not taken yet
     std::unique_ptr<QEntry[]> q;
@@ -278,7 +299,8 @@ static bool join_window(ga_hub *h, Relay *r, uint64_t now_us)
     if (gw == h->group_window.end()) return false;            // :455-457 window == nil
     Window &w = h->windows[gw->second];
     if (!w.is_active) return false;                           // :462-464
-    if (now_us - w.start_us > w.duration_us) return false;    // :467-470 elapsed > WindowDuration
+    const uint64_t elapsed = now_us > w.start_us ? now_us - w.start_us : 0;   // time.Since; a clock behind the window's start counts as 0
+    if (elapsed > w.duration_us) return false;                // :467-470 elapsed > WindowDuration
     bool present = false;
     for (auto &id : w.relays) present |= (id == r->id);
     if (!present) w.relays.push_back(r->id);                  // :481 (map insert: re-joining replaces the entry)
@@ -322,7 +344,7 @@ static int enqueue_chunk(ga_hub *h, Relay *r, const uint8_t *audio, uint32_t nby
     void *dst = nullptr;
     uint64_t off = 0, seq = 0;
     {
-        std::lock_guard<std::mutex> lk(q.claim);
+        std::lock_guard<SpinLock> lk(q.claim);
         if (q.tail - q.head.load(std::memory_order_acquire) >= q.cap) {
             set_error("ga_hub_on_chunk: %llu chunks are waiting for a flush on GPU %u", (unsigned long long)q.cap, r->shard);
             return GA_ERR_RING_FULL;
@@ -605,7 +627,7 @@ extern "C" int ga_hub_poll(ga_hub *h, uint64_t now_us, uint32_t *n_closed)
     std::lock_guard<std::mutex> lk(h->mu);
     std::vector<uint64_t> due;
     for (auto &kv : h->windows)
-        if (kv.second.is_active && now_us - kv.second.start_us >= kv.second.duration_us) due.push_back(kv.first);
+        if (kv.second.is_active && now_us >= kv.second.start_us && now_us - kv.second.start_us >= kv.second.duration_us) due.push_back(kv.first);
     if (n_closed) *n_closed = static_cast<uint32_t>(due.size());
     return arbitrate_windows(h, due);
     GA_GUARD_END
@@ -620,7 +642,7 @@ extern "C" int ga_hub_poll_windows(ga_hub *h, uint64_t now_us, uint64_t *window_
     std::lock_guard<std::mutex> lk(h->mu);
     std::vector<uint64_t> due;
     for (auto &kv : h->windows)
-        if (kv.second.is_active && now_us - kv.second.start_us >= kv.second.duration_us) due.push_back(kv.first);
+        if (kv.second.is_active && now_us >= kv.second.start_us && now_us - kv.second.start_us >= kv.second.duration_us) due.push_back(kv.first);
     if (n_closed) *n_closed = static_cast<uint32_t>(due.size());
     for (size_t k = 0; k < due.size() && k < cap; k++) window_ids[k] = due[k];
     return arbitrate_windows(h, due);
