@@ -97,6 +97,7 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sweep", action="store_true", help="N = 1: skip the cfg2 / cfg4 / cfg5_shard sweep")
+    ap.add_argument("--no-tick", action="store_true", help="N = 1: skip the real-time block (tools/hub_realtime.bin)")
     ap.add_argument("--sweep-steps", type=int, default=5)
     ap.add_argument("--fill-threads", type=int, default=0, help="host threads of the e2e with_fill leg (0 = all)")
     ap.add_argument("--cpu-threads", type=int, default=0)
@@ -787,6 +788,29 @@ def run_e2e(env, w, plan, pcm, arbitration, d_winner, steps):
                         name, n_sub, sub_msgs)}
 
 
+def tick_block(device):
+    """Real-time (tick-mode) evidence through the drop-in path: tools/hub_realtime.bin drives the C++ hub
+    (ga_hub_on_chunk_h from 8 relay threads, ga_hub_flush + ga_hub_poll_windows + ga_hub_fetch_winner_wavs
+    from one batching thread) with 8,192 relays — one GPU's share of the 65,536-stream target — first in
+    real time (20 ms ticks: per-tick and window-close latency), then as fast as it goes (sustained
+    chunks per second; real time needs 409,600 per GPU)."""
+    tool = os.path.join(ROOT, "tools", "hub_realtime.bin")
+    if not os.path.exists(tool):
+        return {"unavailable": "tools/hub_realtime.bin not built"}
+    out = {}
+    for key, extra in (("paced", ["--paced", "1", "--seconds", "3"]), ("saturated", ["--paced", "0", "--seconds", "2"])):
+        try:
+            r = subprocess.run([tool, "--device", str(device), "--streams", "8192", "--threads", "8"] + extra,
+                               capture_output=True, text=True, timeout=120)
+            out[key] = json.loads(r.stdout.strip().splitlines()[-1]) if r.returncode == 0 else \
+                {"failed": r.returncode, "stderr": r.stderr[-300:]}
+        except Exception as e:                      # noqa: BLE001 — the tick block must not take the bench line down
+            out[key] = {"failed": str(e)}
+    out["note"] = ("tick_latency_ms = from a tick's scheduled time (all 8,192 relays start pushing their 20 ms chunk) to its "
+                   "result records being on the host; window_close_ms = ga_hub_poll_windows for the windows due in that tick")
+    return out
+
+
 def main():
     args = parse()
     claim_stdout()
@@ -829,6 +853,8 @@ def main():
                 sweep[name] = keep
                 log("bench: sweep %s done in %.1f s" % (name, time.time() - t0))
             out["configs"] = sweep
+        if not args.no_tick:
+            out["tick"] = tick_block(env.local_rank)
     if env.world > 1:
         env.dist.barrier()
     if env.rank == 0:

@@ -27,6 +27,15 @@ type Config struct {
 
 func lastErr(rc C.int) error { return errors.New(C.GoString(C.ga_last_error())) }
 
+// MaxInflight is ga_config.max_inflight as New sets it: result slots are used round-robin, so the
+// records of ticket t are overwritten by the Submit that returns ticket t+MaxInflight.
+const MaxInflight = 4
+
+var ErrQueueFull = errors.New("gpuaudio: chunk queue full until the next batch tick")
+
+func cu64(v uint64) C.uint64_t { return C.uint64_t(v) }
+func cu32(v uint32) C.uint32_t { return C.uint32_t(v) }
+
 // New is called beside createAudioService (audio_service.go:233-244).
 func New(cfg Config) (*Ctx, error) {
 	cc := C.ga_config{device: C.int32_t(cfg.Device), max_streams: C.uint32_t(cfg.MaxStreams),
@@ -46,13 +55,59 @@ func (x *Ctx) Close() { C.ga_shutdown(x.c) }
 // bytesToFloat32Array; lock-free on the C side.  C never keeps a Go pointer (cgo rule): the
 // destination is C memory, wrapped with unsafe.Slice only for the copy.
 func (x *Ctx) Push(audioData []byte) (uint64, error) {
+	dst, off, err := x.Reserve(len(audioData))
+	if err != nil {
+		return 0, err
+	}
+	copy(dst, audioData)
+	return off, nil
+}
+
+// Reserve is the first half of Push: n bytes of the pinned ring as a Go slice over C memory, and
+// their ring offset.  The batcher reserves under its queue mutex and copies outside it.
+func (x *Ctx) Reserve(n int) ([]byte, uint64, error) {
 	var p unsafe.Pointer
 	var off C.uint64_t
-	if rc := C.ga_ring_reserve(x.c, C.uint64_t(len(audioData)), &p, &off); rc != 0 {
-		return 0, lastErr(rc)
+	if rc := C.ga_ring_reserve(x.c, C.uint64_t(n), &p, &off); rc != 0 {
+		return nil, 0, lastErr(rc)
 	}
-	copy(unsafe.Slice((*byte)(p), len(audioData)), audioData)
-	return uint64(off), nil
+	return unsafe.Slice((*byte)(p), n), uint64(off), nil
+}
+
+// StreamReset frees a stream slot's buffers for its next owner (cleanupRelay, audio_service.go:916-923).
+func (x *Ctx) StreamReset(slot uint32) error {
+	if rc := C.ga_stream_reset(x.c, C.uint32_t(slot)); rc != 0 {
+		return lastErr(rc)
+	}
+	return nil
+}
+
+// WinnerAudio is processWinningRelayAudio's input for MANY winners at once (audio_service.go:590-609):
+// per slot the WAV file float32ToWAV would build (internal/llm/stt_client.go:365-398) and the
+// "sha256:<hex>" fingerprint of its samples (events/voice_event.go:84-88).  One launch + one copy per
+// call; the WAV bytes are copied out of the C-owned staging buffer (valid only until the next call).
+func (x *Ctx) WinnerAudio(slots []uint32, sampleRate int) (wavs [][]byte, hashes []string, err error) {
+	if len(slots) == 0 {
+		return nil, nil, nil
+	}
+	var base *C.uint8_t
+	offs := make([]C.uint64_t, len(slots)+1)
+	dig := make([]byte, 32*len(slots))
+	if rc := C.ga_fetch_wavs(x.c, (*C.uint32_t)(&slots[0]), C.uint32_t(len(slots)), C.uint32_t(sampleRate),
+		&base, &offs[0], (*C.uint8_t)(&dig[0])); rc != 0 {
+		return nil, nil, lastErr(rc)
+	}
+	wavs, hashes = make([][]byte, len(slots)), make([]string, len(slots))
+	for i := range slots {
+		p := unsafe.Add(unsafe.Pointer(base), uintptr(offs[i]))
+		hdr := unsafe.Slice((*byte)(p), 8)
+		size := 8 + int(uint32(hdr[4])|uint32(hdr[5])<<8|uint32(hdr[6])<<16|uint32(hdr[7])<<24) // RIFF size + 8
+		wavs[i] = append([]byte(nil), unsafe.Slice((*byte)(p), size)...)
+		var h [C.GA_AUDIO_HASH_LEN]C.char
+		C.ga_format_audio_hash((*C.uint8_t)(&dig[32*i]), &h[0])
+		hashes[i] = C.GoString(&h[0])
+	}
+	return
 }
 
 type Msg = C.ga_msg       // {ring_offset, nbytes, stream_id, flags}
