@@ -4,7 +4,7 @@
 # Usage: tools/r2_profile.sh <tag>      (writes gpurun_out/<tag>_*)
 tag=${1:-r2a}
 out=gpurun_out
-B="python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline --no-sweep"
+B="python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline --no-sweep --no-tick"
 EXTRA="sm__inst_executed_pipe_alu.sum,sm__inst_executed_pipe_fma.sum,sm__inst_executed_pipe_fmaheavy.sum,sm__inst_executed_pipe_xu.sum,sm__inst_executed_pipe_lsu.sum,sm__inst_executed.sum,sm__cycles_active.avg,sm__cycles_elapsed.max"
 set -x
 $B > $out/${tag}_plain_cfg3.log 2>&1 || exit 1
