@@ -13,9 +13,9 @@
 // A warp owns groups of 32 consecutive messages.  Pass 1 walks the group one message at a time
 // with all 32 lanes: the message's bytes arrive in shared memory by ONE TMA bulk copy (3,840 B,
 // issued one message ahead on a 2-stage mbarrier pipeline), 47 history frames + the message are
-// converted to mono f32 in shared memory, each lane produces 12 CONSECUTIVE outputs from an
-// 88-float register window (stride 36 floats between lanes = 9 x 16 B, odd, so the LDS.128 loads
-// are conflict-free; taps come from the constant bank; 576 FMAs per lane), and the outputs leave
+// converted to mono f32 in shared memory, each lane produces 10 CONSECUTIVE outputs from a
+// 76-float register window (stride 30 floats between lanes = 15 x 8 B, odd, so the 64-bit loads
+// are conflict-free; taps come from the constant bank; 480 FMAs per lane, all 32 lanes busy), and the outputs leave
 // through shared memory as coalesced 16-byte stores.  Pass 2 is lane = message: each lane re-reads
 // ITS message's outputs (still in L2) and runs the reference's strictly sequential float64 chain
 // and the other statistics, so the serial chain costs 1/32 of a warp per message instead of a
@@ -33,7 +33,8 @@ constexpr int kTaps = GA_RESAMPLE_TAPS;          // 48
 constexpr int kHist = kTaps - 1;                 // 47 frames carried between messages
 constexpr int kRsWarps = 4;
 constexpr int kRsMaxFrames = 960;                // frames per message (20 ms at 48 kHz)
-constexpr int kOutPerLane = 12;
+constexpr int kOutPerLane = 10;                  // 32 lanes x 10 outputs = one 20 ms message
+constexpr int kWin = 3 * (kOutPerLane - 1) + kTaps + 1;   // 76 floats: a lane window of 75, +1 when it starts at an odd float
 constexpr int kRsMaxOut = kRsMaxFrames / 3 + 1;
 constexpr int kPad = 48;                         // message frames start at mono[48]: 16-byte aligned rows
 // mono[] holds kPad + kRsMaxFrames floats, padded so the 88-float register windows never run off
@@ -58,15 +59,36 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 
 __constant__ uint32_t c_tap_bits[kTaps] = GA_RESAMPLE_TAP_BITS;
 
-#ifndef GA_PACKED_MONO
-#define GA_PACKED_MONO 1
+#ifndef GA_RS_FMA1
+#define GA_RS_FMA1 1
 #endif
+// mono = (A1(L) + A1(R)) * 0.5f for one interleaved stereo frame (L in the low half, R in the high half).
+//
+// A1(v) = float32(v) / 32767.0f is an IEEE division (audio_service.go:1078).  For the 65,536 possible
+// inputs it can be had from ONE fused multiply-add:  with a = v * 2^-15 (exact),
+//     RN(v / 32767) == fma(a, c, a),   c = 2^-15 + 2^-30   (exactly representable; 32768/32767 = 1 + c + 2^-45 + …)
+// — a * c is exact inside the FMA and the one rounding sees a * (1 + c), whose relative distance from
+// the true quotient (2^-45) never reaches a rounding boundary of the result; verified for all 65,536
+// values against the division (exact rational arithmetic, and tests/test_gpu_resample.py on the GPU).
+// Scaling by a power of two commutes with rounding, so the halves are taken first:
+//     (A1(L) + A1(R)) * 0.5f == fma(l, c, l) + fma(r, c, r)   with l = L * 2^-16, r = R * 2^-16,
+// and v * 2^-16 costs nothing: the int16, biased by 0x8000, is spliced under the exponent of 2^7
+// (ulp 2^-16) and 128.5 is subtracted.  Per frame: LOP3, 2 PRMT, FADD2, FFMA2, FADD.
 __device__ __forceinline__ float mono_of(uint32_t lr)
 {
-    // lr = one interleaved stereo frame: L in the low half, R in the high half
     const uint32_t x = lr ^ 0x80008000u;
-#if GA_PACKED_MONO
-    // both channels per instruction (FADD2 / FMUL2 / FFMA2: two independent IEEE operations each)
+#if GA_RS_FMA1
+    unsigned long long v, q, kb, kc;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(v) : "r"(__byte_perm(x, 0x43000000u, 0x7610)), "r"(__byte_perm(x, 0x43000000u, 0x7632)));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(kb) : "f"(-128.5f));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(kc) : "f"(0x1.0002p-15f));
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(v) : "l"(v), "l"(kb));
+    asm("fma.rn.f32x2 %0, %1, %2, %1;" : "=l"(q) : "l"(v), "l"(kc));
+    float l, r;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(l), "=f"(r) : "l"(q));
+    return __fadd_rn(l, r);
+#else
+    // the division as multiply + residual correction (common.cuh pcm_to_f32), both channels per instruction
     const float rcp = 1.0f / 32767.0f;
     unsigned long long v, q0, e, q, kb, kr, kn;
     asm("mov.b64 %0, {%1, %2};" : "=l"(v) : "r"(__byte_perm(x, 0x4B000000u, 0x7610)), "r"(__byte_perm(x, 0x4B000000u, 0x7632)));
@@ -80,10 +102,6 @@ __device__ __forceinline__ float mono_of(uint32_t lr)
     float l, r;
     asm("mov.b64 {%0, %1}, %2;" : "=f"(l), "=f"(r) : "l"(q));
     return __fmul_rn(__fadd_rn(l, r), 0.5f);
-#else
-    const float l = __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7610)) - 8421376.0f;
-    const float r = __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7632)) - 8421376.0f;
-    return __fmul_rn(__fadd_rn(pcm_to_f32(l), pcm_to_f32(r)), 0.5f);
 #endif
 }
 
@@ -196,41 +214,46 @@ resample48_kernel(const ResampleParams p)
             }
             __syncwarp();
 
-            // FIR: lane produces outputs [12*lane, 12*lane + 12)
+            // FIR: lane produces outputs [10*lane, 10*lane + 10) — 32 lanes x 10 = the 320 outputs of a
+            // 20 ms message, every lane busy.  Its window (75 floats) starts at an even float for every
+            // lane (lane stride 30), so it is read with 64-bit loads: 15 eight-byte words between lanes,
+            // odd, hence conflict-free.
             const uint32_t o0 = kOutPerLane * lane;
             if (o0 < n_out) {
-                // newest tap of output o is mono[top0 + 3*o]; oldest is 47 below.  Window base (aligned down to 4):
+                // newest tap of output o is mono[top0 + 3*o]; oldest is 47 below.  Window base (aligned down to 2):
                 const uint32_t lo_idx = top0 + 3 * o0 - kHist;              // oldest float needed
-                const uint32_t wbase4 = lo_idx & ~3u;
-                const uint32_t sh = lo_idx - wbase4;                        // 0..3
-                float win[88];
-                const float4 *w4 = reinterpret_cast<const float4 *>(mono + wbase4);
+                const uint32_t wbase2 = lo_idx & ~1u;
+                const uint32_t sh = lo_idx - wbase2;                        // 0 or 1, the same for every lane
+                float win[kWin];
+                const float2 *w2 = reinterpret_cast<const float2 *>(mono + wbase2);
 #pragma unroll
-                for (int k = 0; k < 22; k++) {
-                    const float4 t = w4[k];
-                    win[4 * k] = t.x; win[4 * k + 1] = t.y; win[4 * k + 2] = t.z; win[4 * k + 3] = t.w;
+                for (int k = 0; k < kWin / 2; k++) {
+                    const float2 t = w2[k];
+                    win[2 * k] = t.x; win[2 * k + 1] = t.y;
                 }
                 float acc[kOutPerLane];
 #pragma unroll
                 for (int o = 0; o < kOutPerLane; o++) acc[o] = 0.0f;
-                // the window offset `sh` is warp-uniform (36*lane is a multiple of 4) and takes only 4
-                // values: a switch makes every win[] index a compile-time constant (registers, not local memory)
+                // the window offset `sh` is warp-uniform and takes two values: a branch makes every
+                // win[] index a compile-time constant (registers, not local memory)
 #define GA_FIR(SH)                                                                              \
     _Pragma("unroll") for (int k = 0; k < kTaps; k++) {                                         \
         const float h = __uint_as_float(c_tap_bits[k]);                                         \
         _Pragma("unroll") for (int o = 0; o < kOutPerLane; o++)                                 \
             acc[o] = __fmaf_rn(h, win[(SH) + 3 * o + kHist - k], acc[o]);                       \
     }
-                switch (sh) {
-                    case 0: GA_FIR(0) break;
-                    case 1: GA_FIR(1) break;
-                    case 2: GA_FIR(2) break;
-                    default: GA_FIR(3) break;
-                }
+                if (sh == 0) { GA_FIR(0) } else { GA_FIR(1) }
 #undef GA_FIR
+                // outputs leave through shared memory: pairs as 64-bit stores (5 words between lanes: conflict-free)
+                if (o0 + kOutPerLane <= n_out) {
 #pragma unroll
-                for (int o = 0; o < kOutPerLane; o++)
-                    if (o0 + o < n_out) ybuf[o0 + o] = acc[o];
+                    for (int o = 0; o < kOutPerLane; o += 2)
+                        *reinterpret_cast<float2 *>(ybuf + o0 + o) = make_float2(acc[o], acc[o + 1]);
+                } else {
+#pragma unroll
+                    for (int o = 0; o < kOutPerLane; o++)
+                        if (o0 + o < n_out) ybuf[o0 + o] = acc[o];
+                }
             }
             __syncwarp();
 

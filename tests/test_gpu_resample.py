@@ -171,6 +171,21 @@ def test_saved_history_is_not_overwritten_while_an_earlier_chunk_still_needs_it(
             assert bits(r["peak"]) == bits(st.peak)
 
 
+def test_every_int16_value_in_both_channels(ctx48):
+    """The kernel takes A1's division (audio_service.go:1078) as one fused multiply-add per channel
+    (csrc/resample.cu mono_of); that is exact only because it was checked for every input, so every
+    int16 value goes through both channels here, against the oracle's plain division."""
+    rng = np.random.default_rng(33)
+    left = rng.permutation(np.arange(-32768, 32768)).astype("<i2")
+    right = np.concatenate([left[::-1][1:], left[:1]]).astype("<i2")       # a different value beside each
+    pcm = np.stack([left, right], axis=1)
+    chunks = [pcm[i:i + 960].tobytes() for i in range(0, len(pcm), 960)]
+    fl = np.zeros(len(chunks), np.uint32); fl[0] = L.MSG_FIRST
+    ctx48.ingest(chunks, np.full(len(chunks), 21, np.uint32), fl)
+    want = np.concatenate(oracle_stream(chunks))
+    assert np.array_equal(bits(ctx48.fetch_samples(21)), bits(want))
+
+
 def test_48k_boundary_rules(ctx48):
     with pytest.raises(L.GpuAudioError) as e:
         ctx48.ingest([b"\x00" * 3844], [1], [L.MSG_FIRST])
