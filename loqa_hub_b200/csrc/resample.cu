@@ -23,6 +23,7 @@
 // saving); no tensor cores: a 48-tap FIR at 16 k outputs/s is 1.5 MFLOP per audio-second, four
 // orders below the HBM cost.
 #include <cstring>
+#include <type_traits>
 
 #include "common.cuh"
 #include "../../include/gpuaudio_taps.h"
@@ -105,13 +106,14 @@ __device__ __forceinline__ float mono_of(uint32_t lr)
 #endif
 }
 
-// number of outputs of a message of nfr frames that starts at absolute frame n0, and the mono[]
-// index of output 0's newest tap: outputs are the M with n0 <= 3M+2 < n0 + nfr
-__device__ __forceinline__ uint32_t out_count(uint64_t n0, uint32_t nfr, uint32_t *top0)
+// Outputs are the M with n0 <= 3M+2 < n0 + nfr.  With r0 = n0 mod 3 and M = n0/3 + j that is
+// 0 <= 3j + 2 - r0 < nfr: the message yields floor((nfr + r0) / 3) outputs and the newest tap of
+// its first output is frame 2 - r0 of the message — only n0 mod 3 matters, which every lane works
+// out once for its own message of the group (one 64-bit modulo instead of two per message and lane).
+__device__ __forceinline__ uint32_t out_count(uint32_t r0, uint32_t nfr, uint32_t *top0)
 {
-    const uint64_t m_first = n0 / 3, n1 = n0 + nfr;
-    if (top0) *top0 = static_cast<uint32_t>(3 * m_first + 2 - n0) + kPad;
-    return (n1 >= 3 * m_first + 3) ? static_cast<uint32_t>((n1 - 3 * m_first - 3) / 3 + 1) : 0u;
+    if (top0) *top0 = 2u - r0 + kPad;
+    return (nfr + r0) / 3u;
 }
 
 struct ResampleParams {
@@ -152,6 +154,7 @@ resample48_kernel(const ResampleParams p)
         ga_rdesc dl;
         memset(&dl, 0, sizeof dl);
         if (static_cast<uint32_t>(lane) < cnt) dl = p.desc[base + lane];
+        const uint32_t r0_l = static_cast<uint32_t>(dl.n0 % 3ull);
         constexpr uint32_t FULL = 0xffffffffu;
 
         // one bulk copy per message, issued one message ahead
@@ -188,13 +191,12 @@ resample48_kernel(const ResampleParams p)
             ga_rdesc d;
             d.in_off = 0;
             d.out_off = __shfl_sync(FULL, dl.out_off, i);
-            d.n0 = __shfl_sync(FULL, dl.n0, i);
             d.nbytes = __shfl_sync(FULL, dl.nbytes, i);
-            d.stream_id = __shfl_sync(FULL, dl.stream_id, i);
-            d.flags = __shfl_sync(FULL, dl.flags, i);
             const uint32_t nfr = min(d.nbytes >> 2, static_cast<uint32_t>(kRsMaxFrames));   // a partial frame is dropped
             uint32_t top0;
-            const uint32_t n_out = out_count(d.n0, nfr, &top0);
+            const uint32_t n_out = out_count(__shfl_sync(FULL, r0_l, i), nfr, &top0);
+            // the usual message: 20 ms = 960 frames -> 320 outputs at a 16-byte aligned place in the arena
+            const bool std_msg = nfr == kRsMaxFrames && n_out == kRsMaxFrames / 3 && (d.out_off & 3ull) == 0;
 
             // history: the 47 frames before the message.  The loads for message i+1 are issued now
             // and consumed one iteration later, so their latency hides behind this message's work.
@@ -206,11 +208,22 @@ resample48_kernel(const ResampleParams p)
 
             mono[1 + lane] = hsrc ? mono_of(h0) : 0.0f;
             if (lane + 32 < kHist) mono[33 + lane] = hsrc ? mono_of(h1) : 0.0f;
-            const uint32_t nvec = (nfr + 3) >> 2;
+            if (nfr == kRsMaxFrames) {                          // 240 vectors of 4 frames: 7.5 per lane, no loop
+#pragma unroll
+                for (int it = 0; it < kRsMaxFrames / 128 + 1; it++) {
+                    const uint32_t v = lane + 32 * it;
+                    if (it < kRsMaxFrames / 128 || v < kRsMaxFrames / 4) {
+                        const uint4 q = reinterpret_cast<const uint4 *>(msg)[v];
+                        reinterpret_cast<float4 *>(mono + kPad)[v] = make_float4(mono_of(q.x), mono_of(q.y), mono_of(q.z), mono_of(q.w));
+                    }
+                }
+            } else {
+                const uint32_t nvec = (nfr + 3) >> 2;
 #pragma unroll 2
-            for (uint32_t v = lane; v < nvec; v += 32) {        // frames past nfr in the last vector are never read
-                const uint4 q = reinterpret_cast<const uint4 *>(msg)[v];
-                reinterpret_cast<float4 *>(mono + kPad)[v] = make_float4(mono_of(q.x), mono_of(q.y), mono_of(q.z), mono_of(q.w));
+                for (uint32_t v = lane; v < nvec; v += 32) {    // frames past nfr in the last vector are never read
+                    const uint4 q = reinterpret_cast<const uint4 *>(msg)[v];
+                    reinterpret_cast<float4 *>(mono + kPad)[v] = make_float4(mono_of(q.x), mono_of(q.y), mono_of(q.z), mono_of(q.w));
+                }
             }
             __syncwarp();
 
@@ -259,7 +272,14 @@ resample48_kernel(const ResampleParams p)
 
             // coalesced store of the resampled samples
             float *out = p.samples + d.out_off;
-            if ((d.out_off & 3ull) == 0) {
+            if (std_msg) {                                      // 80 vectors: 2.5 per lane, no loop
+#pragma unroll
+                for (int it = 0; it < 3; it++) {
+                    const uint32_t v = lane + 32 * it;
+                    if (it < 2 || v < kRsMaxFrames / 12)
+                        *reinterpret_cast<float4 *>(out + 4 * v) = reinterpret_cast<const float4 *>(ybuf)[v];
+                }
+            } else if ((d.out_off & 3ull) == 0) {
                 const uint32_t n4 = n_out >> 2;
                 for (uint32_t v = lane; v < n4; v += 32) {
                     const float4 t = reinterpret_cast<const float4 *>(ybuf)[v];
@@ -283,19 +303,20 @@ resample48_kernel(const ResampleParams p)
             const uint32_t mi = base + lane;
             const ga_rdesc &d = dl;
             const uint32_t nfr = min(d.nbytes >> 2, static_cast<uint32_t>(kRsMaxFrames));
-            const uint32_t n_out = mine ? out_count(d.n0, nfr, nullptr) : 0u;
+            const uint32_t n_out = mine ? out_count(r0_l, nfr, nullptr) : 0u;
             const float *y = p.samples + d.out_off;
             double msg_sum = 0.0, frm_sum = 0.0;
             uint32_t nz = 0, fnz = 0, fn = 0, fidx = 0;
             float pk = 0.0f, fpk = 0.0f;
-            auto step = [&](float v) {
+            // wf: per-frame records wanted (compile-time, so the common no-frames case carries no test per sample)
+            auto step = [&](float v, auto wf) {
                 const double q = sq_f64(v);
                 msg_sum += q;
                 const uint32_t z = (v != 0.0f);
                 nz += z;
                 const float a = fabsf(v);
                 pk = fmaxf(pk, a);
-                if (p.frames) {
+                if constexpr (decltype(wf)::value) {
                     frm_sum += q; fnz += z; fpk = fmaxf(fpk, a);
                     if (++fn == GA_FRAME_SAMPLES) {
                         ga_frame f;
@@ -306,6 +327,29 @@ resample48_kernel(const ResampleParams p)
                     }
                 }
             };
+            // c samples of this lane's row of a staged slice
+            auto consume = [&](const float4 *row, uint32_t c, auto wf) {
+                if (c == kP2Slice) {
+#pragma unroll
+                    for (int k = 0; k < kP2Slice / 4; k++) {
+                        const float4 t = row[k];
+                        step(t.x, wf); step(t.y, wf); step(t.z, wf); step(t.w, wf);
+                    }
+                    return;
+                }
+                uint32_t k = 0;
+                for (; k + 4 <= c; k += 4) {
+                    const float4 t = row[k >> 2];
+                    step(t.x, wf); step(t.y, wf); step(t.z, wf); step(t.w, wf);
+                }
+                if (k < c) {
+                    const float4 t = row[k >> 2];
+                    step(t.x, wf);
+                    if (k + 1 < c) step(t.y, wf);
+                    if (k + 2 < c) step(t.z, wf);
+                }
+            };
+            const bool with_frames = p.frames != nullptr;
             // The outputs were written cooperatively in pass 1 and are read back per lane here.  Each
             // lane reading its own row from L2 exposes the full memory latency once per 16 bytes, so
             // the rows come back through shared memory instead: slices of 32 samples of all 32 messages,
@@ -337,17 +381,8 @@ resample48_kernel(const ResampleParams p)
                     if (lo < n_out) {
                         const uint32_t c = min(n_out - lo, static_cast<uint32_t>(kP2Slice));
                         const float4 *row = reinterpret_cast<const float4 *>(wbase + (sl & 1u) * kP2BufBytes + lane * kP2RowStride);
-                        uint32_t k = 0;
-                        for (; k + 4 <= c; k += 4) {
-                            const float4 t = row[k >> 2];
-                            step(t.x); step(t.y); step(t.z); step(t.w);
-                        }
-                        if (k < c) {
-                            const float4 t = row[k >> 2];
-                            step(t.x);
-                            if (k + 1 < c) step(t.y);
-                            if (k + 2 < c) step(t.z);
-                        }
+                        if (with_frames) consume(row, c, std::true_type{});
+                        else consume(row, c, std::false_type{});
                     }
                     __syncwarp();
                     if (sl + 2 < n_slices) issue_slice(sl + 2);
@@ -355,14 +390,19 @@ resample48_kernel(const ResampleParams p)
                 // the next group's PCM arrives in these buffers through the TMA (async proxy)
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             } else if (mine) {
+                // rare: unaligned outputs or short messages — straight from L2, always with the frame test
                 uint32_t k = 0;
                 if ((d.out_off & 3ull) == 0) {
                     for (; k + 4 <= n_out; k += 4) {
                         const float4 t = __ldcg(reinterpret_cast<const float4 *>(y + k));
-                        step(t.x); step(t.y); step(t.z); step(t.w);
+                        if (with_frames) { step(t.x, std::true_type{}); step(t.y, std::true_type{}); step(t.z, std::true_type{}); step(t.w, std::true_type{}); }
+                        else { step(t.x, std::false_type{}); step(t.y, std::false_type{}); step(t.z, std::false_type{}); step(t.w, std::false_type{}); }
                     }
                 }
-                for (; k < n_out; k++) step(__ldcg(y + k));
+                for (; k < n_out; k++) {
+                    if (with_frames) step(__ldcg(y + k), std::true_type{});
+                    else step(__ldcg(y + k), std::false_type{});
+                }
             }
             if (mine) {
                 if (p.frames && fn) {
