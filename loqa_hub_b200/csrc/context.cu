@@ -197,6 +197,11 @@ static_assert(sizeof(ga_config) == 64, "ga_config layout");
 static_assert(sizeof(ga_sha_state) == 128, "ga_sha_state layout");
 
 static int arb_reserve(ga_ctx *ctx, size_t need);
+namespace ga {
+static int win_reserve(ga_ctx *ctx, size_t need);
+static int winners_impl(ga_ctx *ctx, const uint32_t *stream_ids, uint32_t n, bool want_wav, uint32_t sample_rate,
+                        bool want_digest, const uint8_t **base, uint64_t *wav_off, const uint8_t **digests);
+}
 
 extern "C" int ga_init(const ga_config *cfg, ga_ctx **out)
 {
@@ -294,6 +299,26 @@ extern "C" int ga_init(const ga_config *cfg, ga_ctx **out)
     GA_ALLOC_TRY(cudaStreamCreateWithFlags(&c->aux, cudaStreamNonBlocking));
     GA_ALLOC_TRY(cudaEventCreateWithFlags(&c->aux_ev, cudaEventDisableTiming));
     if ((cfg->mode & GA_DO_CONVERT) && arb_reserve(c, 26ull * cfg->max_streams + 4096) != GA_OK) { destroy(c); return GA_ERR_NOMEM; }
+    if (cfg->mode & GA_DO_CONVERT) {
+        // The winner path (ga_fetch_wavs / ga_samples_digests) runs at window close, in real time: its
+        // staging is sized here for a window close of every eighth stream with its wake-word buffer and
+        // as much speech again (it still grows on demand), and its kernels are launched once on an
+        // empty stream so that neither an allocation nor a module load lands in the first window close.
+        const size_t per = 44 + 8 * static_cast<size_t>(cfg->wake_samples_max) + 32;
+        const size_t want = std::min<size_t>(512ull * cfg->max_streams + per * (cfg->max_streams / 8 + 1), 96ull << 20);
+        if (win_reserve(c, want) != GA_OK) { destroy(c); return GA_ERR_NOMEM; }
+        const uint32_t sid = 0;
+        const uint8_t *b = nullptr, *dg = nullptr;
+        uint64_t off[2];
+        if (winners_impl(c, &sid, 1, true, 16000, true, &b, off, &dg) != GA_OK) { destroy(c); return GA_ERR_CUDA; }
+        // the same for the window-close kernels (ga_arbitrate): one window of one stream without audio
+        const uint32_t seg[2] = {0, 1};
+        const uint8_t st_in = GA_RELAY_CONTENDING;
+        uint8_t st_out = 0;
+        uint32_t win = 0;
+        double sc = 0.0;
+        if (ga_arbitrate(c, seg, 1, &sid, &st_in, &win, &sc, &st_out) != GA_OK) { destroy(c); return GA_ERR_CUDA; }
+    }
     *out = c;
     return GA_OK;
     GA_GUARD_END
