@@ -806,7 +806,8 @@ def tick_block(device):
                 {"failed": r.returncode, "stderr": r.stderr[-300:]}
         except Exception as e:                      # noqa: BLE001 — the tick block must not take the bench line down
             out[key] = {"failed": str(e)}
-    out["note"] = ("tick_latency_ms = from a tick's scheduled time (all 8,192 relays start pushing their 20 ms chunk) to its "
+    out["note"] = ("steady_chunks_per_s = rate once every collision group has started (the groups' utterances start spread "
+                   "over the first 50 ticks; real time is 409,600 chunks/s for 8,192 relays); tick_latency_ms = from a tick's scheduled time (all 8,192 relays start pushing their 20 ms chunk) to its "
                    "result records being on the host; window_close_ms = ga_hub_poll_windows for the windows due in that tick")
     return out
 

@@ -133,6 +133,8 @@ int main(int argc, char **argv)
     };
 
     std::vector<double> tick_lat, flush_ms, close_ms, fetch_ms;
+    double ramp_t = 0.0, last_flush_t = 0.0;
+    uint64_t ramp_ingested = 0;
     uint64_t ingested = 0, windows_closed = 0, wav_bytes_total = 0, ticks_done = 0, winners_wrong = 0;
     std::vector<uint64_t> closed(streams / group + 1);
     std::vector<const uint8_t *> wav_ptrs(closed.size());
@@ -158,6 +160,8 @@ int main(int argc, char **argv)
                 k = ready == ~0ull ? k : ready;
             }
             ticks_done = k;
+            if (k >= 50 && ramp_t == 0.0) { ramp_t = b; ramp_ingested = ingested; }   // every group has started by tick 50
+            last_flush_t = b;
             // the window timer: virtual time of the slowest relay thread
             uint32_t nc = 0;
             const double c = now_s();
@@ -190,19 +194,20 @@ int main(int argc, char **argv)
     for (auto &t : th) t.join();
     bt.join();
     const double wall = now_s() - t0;
+    const double steady = (ramp_t > 0.0 && last_flush_t > ramp_t) ? (ingested - ramp_ingested) / (last_flush_t - ramp_t) : 0.0;
     uint32_t n = 0;
     ga_hub_flush(hub, &n);
     ingested += n;
 
     printf("{\"tool\": \"hub_realtime\", \"paced\": %d, \"streams\": %u, \"relay_threads\": %u, \"seconds\": %.3f, "
-           "\"chunks_pushed\": %llu, \"chunks_ingested\": %llu, \"chunks_per_s\": %.0f, \"audio_s_per_s\": %.0f, "
+           "\"chunks_pushed\": %llu, \"chunks_ingested\": %llu, \"chunks_per_s\": %.0f, \"steady_chunks_per_s\": %.0f, \"audio_s_per_s\": %.0f, "
            "\"ticks\": %llu, \"backpressure_retries\": %llu, "
            "\"tick_latency_ms\": {\"p50\": %.3f, \"p99\": %.3f, \"max\": %.3f, \"n\": %zu}, "
            "\"flush_ms\": {\"p50\": %.3f, \"p99\": %.3f, \"n\": %zu}, "
            "\"window_close_ms\": {\"p50\": %.3f, \"p99\": %.3f, \"n\": %zu, \"windows\": %llu, \"wrong_winners\": %llu}, "
            "\"winner_fetch_ms\": {\"p50\": %.3f, \"p99\": %.3f, \"n\": %zu, \"wav_bytes\": %llu}}\n",
            paced, streams, threads, wall, (unsigned long long)pushed.load(), (unsigned long long)ingested,
-           ingested / wall, ingested * 0.02 / wall, (unsigned long long)ticks_done, (unsigned long long)backpressure.load(),
+           ingested / wall, steady, ingested * 0.02 / wall, (unsigned long long)ticks_done, (unsigned long long)backpressure.load(),
            pct(tick_lat, 0.5), pct(tick_lat, 0.99), pct(tick_lat, 1.0), tick_lat.size(),
            pct(flush_ms, 0.5), pct(flush_ms, 0.99), flush_ms.size(),
            pct(close_ms, 0.5), pct(close_ms, 0.99), close_ms.size(), (unsigned long long)windows_closed,
