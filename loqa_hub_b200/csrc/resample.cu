@@ -60,6 +60,9 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 
 __constant__ uint32_t c_tap_bits[kTaps] = GA_RESAMPLE_TAP_BITS;
 
+#ifndef GA_RS_ROLLCONV
+#define GA_RS_ROLLCONV 1
+#endif
 #ifndef GA_RS_FMA1
 #define GA_RS_FMA1 1
 #endif
@@ -209,7 +212,11 @@ resample48_kernel(const ResampleParams p)
             mono[1 + lane] = hsrc ? mono_of(h0) : 0.0f;
             if (lane + 32 < kHist) mono[33 + lane] = hsrc ? mono_of(h1) : 0.0f;
             if (nfr == kRsMaxFrames) {                          // 240 vectors of 4 frames: 7.5 per lane, no loop
+#if GA_RS_ROLLCONV
+#pragma unroll 1
+#else
 #pragma unroll
+#endif
                 for (int it = 0; it < kRsMaxFrames / 128 + 1; it++) {
                     const uint32_t v = lane + 32 * it;
                     if (it < kRsMaxFrames / 128 || v < kRsMaxFrames / 4) {
