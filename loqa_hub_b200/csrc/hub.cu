@@ -70,7 +70,7 @@ struct QMsg {
     uint32_t gen;                    // the slot's generation when the chunk arrived
 };
 
-struct QEntry {
+struct alignas(64) QEntry {          // one cache line per entry: neighbouring entries are written by different threads
     QMsg v;
     std::atomic<uint64_t> ready{0};  // sequence number + 1 once v is published
 };
@@ -97,9 +97,9 @@ struct SpinLock {
 };
 
 struct ShardQueue {
-    SpinLock claim;                  // held for {ring reservation, sequence number} only
-    uint64_t tail = 0;               // next sequence number (under claim)
-    std::atomic<uint64_t> head{0};   // first sequence number the flush has not taken yet
+    alignas(64) SpinLock claim;      // held for {ring reservation, sequence number} only
+    uint64_t tail = 0;               // next sequence number (under claim; same cache line as the lock)
+    alignas(64) std::atomic<uint64_t> head{0};   // first sequence number the flush has not taken yet (written by the flush only)
     std::unique_ptr<QEntry[]> q;
     uint64_t cap = 0;                // power of two
     std::vector<QMsg> carry;         // taken off the queue but not submitted (flush only)
