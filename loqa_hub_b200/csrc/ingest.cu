@@ -82,7 +82,7 @@ struct IngestParams {
 #define GA_PACKED_CONVERT 1
 #endif
 #ifndef GA_SHA_ROLLED
-#define GA_SHA_ROLLED true
+#define GA_SHA_ROLLED 1
 #endif
 #ifndef GA_ROUND_IMAD
 #define GA_ROUND_IMAD false
@@ -420,7 +420,7 @@ ingest_kernel(const IngestParams p, const __grid_constant__ CUtensorMap tmap)
                         }
                         // next to the conversion code the unrolled rounds overflow the 32 KB instruction
                         // cache: fused instantiations run rounds 16..63 as a 3-pass loop
-                        sha256_compress<GA_SCHED_IMAD, GA_ROUND_IMAD, GA_SHA_ROLLED && (kFeat || kLaneStore || kCoop)>(sha, w, p.one);
+                        sha256_compress<GA_SCHED_IMAD, GA_ROUND_IMAD, (kFeat || kLaneStore || kCoop) ? GA_SHA_ROLLED : 0>(sha, w, p.one);
                     }
                 }
                 if (kFeat && last && frm.n) emit_frame();

@@ -72,7 +72,7 @@ static __constant__ uint32_t ga_sha_k[64] = {
     0x19a4c116u, 0x1e376c08u, 0x2748774cu, 0x34b0bcb5u, 0x391c0cb3u, 0x4ed8aa4au, 0x5b9cca4fu, 0x682e6ff3u,
     0x748f82eeu, 0x78a5636fu, 0x84c87814u, 0x8cc70208u, 0x90befffau, 0xa4506cebu, 0xbef9a3f7u, 0xc67178f2u};
 
-template <bool kImad = false, bool kImadRound = false, bool kRolled = false>
+template <bool kImad = false, bool kImadRound = false, int kRolled = 0>
 __device__ __forceinline__ void sha256_compress(Sha256State &s, uint32_t (&w)[16], uint32_t one = 1u)
 {
     uint32_t a = s.h[0], b = s.h[1], c = s.h[2], d = s.h[3];
@@ -94,7 +94,22 @@ __device__ __forceinline__ void sha256_compress(Sha256State &s, uint32_t (&w)[16
 
     GA_R8(0x428a2f98u, 0x71374491u, 0xb5c0fbcfu, 0xe9b5dba5u, 0x3956c25bu, 0x59f111f1u, 0x923f82a4u, 0xab1c5ed5u, 0)
     GA_R8(0xd807aa98u, 0x12835b01u, 0x243185beu, 0x550c7dc3u, 0x72be5d74u, 0x80deb1feu, 0x9bdc06a7u, 0xc19bf174u, 8)
-    if (kRolled) {
+    if (kRolled == 2) {
+        // rounds 16..31 straight, 32..63 as two passes over the 16-round body: two thirds of the
+        // unrolled form's code, one loop back-edge less than the three-pass form
+        GA_S8(16)
+        GA_R8(0xe49b69c1u, 0xefbe4786u, 0x0fc19dc6u, 0x240ca1ccu, 0x2de92c6fu, 0x4a7484aau, 0x5cb0a9dcu, 0x76f988dau, 16)
+        GA_S8(24)
+        GA_R8(0x983e5152u, 0xa831c66du, 0xb00327c8u, 0xbf597fc7u, 0xc6e00bf3u, 0xd5a79147u, 0x06ca6351u, 0x14292967u, 24)
+#pragma unroll 1
+        for (int r = 32; r < 64; r += 16) {
+            const uint32_t *kk = ga_sha_k + r;
+            GA_S8(16)
+            GA_R8(kk[0], kk[1], kk[2], kk[3], kk[4], kk[5], kk[6], kk[7], 16)
+            GA_S8(24)
+            GA_R8(kk[8], kk[9], kk[10], kk[11], kk[12], kk[13], kk[14], kk[15], 24)
+        }
+    } else if (kRolled) {
         // rounds 16..63 as three passes over one 16-round body (the register roles of a..h and
         // the 16-word window both return to their start after 16 rounds); the round constants
         // come from the constant bank.  A third of the code of the fully unrolled form — for
