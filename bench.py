@@ -99,7 +99,8 @@ def parse():
     ap.add_argument("--no-sweep", action="store_true", help="N = 1: skip the cfg2 / cfg4 / cfg5_shard sweep")
     ap.add_argument("--no-tick", action="store_true", help="N = 1: skip the real-time block (tools/hub_realtime.bin)")
     ap.add_argument("--sweep-steps", type=int, default=5)
-    ap.add_argument("--fill-threads", type=int, default=0, help="host threads of the e2e with_fill leg (0 = all)")
+    ap.add_argument("--fill-threads", type=int, default=4,
+                    help="host threads of the e2e with_fill leg (0 = all; numpy copies into the pinned ring stop scaling at ~4)")
     ap.add_argument("--cpu-threads", type=int, default=0)
     args = ap.parse_args()
     if args.workload is None:
@@ -714,15 +715,21 @@ def run_e2e(env, w, plan, pcm, arbitration, d_winner, steps):
     pool = ThreadPoolExecutor(nfill)
     cuts = [sub_bytes * i // nfill // 64 * 64 for i in range(nfill)] + [sub_bytes]
 
-    def fill_block(view, src):          # numpy releases the GIL for large copies: nfill memcpys in parallel
-        list(pool.map(lambda i: np.copyto(view[cuts[i]:cuts[i + 1]], src[cuts[i]:cuts[i + 1]]), range(nfill)))
+    def start_fill(j):                  # reserve sub-batch j and copy its bytes in with nfill threads (numpy releases the GIL)
+        view, off = ctx.reserve(sub_bytes)
+        src = host_pcm[(j % n_host) * sub_bytes:(j % n_host + 1) * sub_bytes]
+        return off, [pool.submit(np.copyto, view[cuts[i]:cuts[i + 1]], src[cuts[i]:cuts[i + 1]]) for i in range(nfill)]
 
     def one_step(fill):
         tickets = []
+        nxt = start_fill(0) if fill else None
         for j in range(n_sub):
-            view, off = ctx.reserve(sub_bytes)
-            if fill:                                    # the relays' bytes land in the ring
-                fill_block(view, host_pcm[(j % n_host) * sub_bytes:(j % n_host + 1) * sub_bytes])
+            if fill:                                    # the relays' bytes land in the ring while the GPU works on
+                off, futs = nxt                         # the sub-batches before (as relay goroutines would do it)
+                for f in futs:
+                    f.result()
+            else:
+                _, off = ctx.reserve(sub_bytes)
             t = C.c_uint64()
             if ticks:
                 L.check(lib.ga_submit_ticks(ctx._h, off, tps, S, chunk, L.ptr(ids), L.ptr(tick_flags[j]), C.byref(t)))
@@ -733,6 +740,8 @@ def run_e2e(env, w, plan, pcm, arbitration, d_winner, steps):
             tickets.append(t.value)
             if len(tickets) == 4:
                 wait(tickets.pop(0))
+            if fill and j + 1 < n_sub:
+                nxt = start_fill(j + 1)
         for t in tickets:
             wait(t)
         arbitration(arena_ptr.value)
@@ -781,7 +790,8 @@ def run_e2e(env, w, plan, pcm, arbitration, d_winner, steps):
             "with_fill": {"value": audio_s * fill_steps / dt_fill, "ms_per_step": 1e3 * dt_fill / fill_steps,
                           "steps": fill_steps, "fill_threads": nfill,
                           "note": "as e2e, plus every step's bytes copied from ordinary host memory into the pinned "
-                                  "ring (ga_ring_reserve + memcpy) inside the timed region"},
+                                  "ring (ga_ring_reserve + memcpy by fill_threads threads) inside the timed region, the copy "
+                                  "of sub-batch j+1 running while sub-batch j is submitted"},
             "note": "host clock around %s/ga_wait_view/arbitration/D2H of winners; chunks already in the pinned ring "
                     "(a relay's goroutine copies them there as they arrive; see with_fill); %d submits of %d msgs "
                     "per step, 4 tickets in flight; h2d_ceiling = bare concurrent pinned copies in this run" % (
