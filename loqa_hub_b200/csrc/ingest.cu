@@ -174,6 +174,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, (MODE == 7u) ? 5 : 0)
 ingest_kernel(const IngestParams p, const __grid_constant__ CUtensorMap tmap)
 {
     constexpr bool kTmap = (COOP & 4) != 0;                                       // 2-D TMA staging (uniform batches)
+    constexpr bool kNoFrames = (COOP & 8) != 0;                                   // launched without frame records: no per-frame energy chain
     constexpr bool kOutTile = (MODE & GA_DO_CONVERT) != 0 && (COOP & 1) == 1;
     using L = TileSmem<CH, STAGES, kTmap, kOutTile>;
     constexpr bool kCoop = (MODE & GA_DO_CONVERT) != 0 && (COOP & 1) == 1;      // cooperative store pass
@@ -273,7 +274,7 @@ ingest_kernel(const IngestParams p, const __grid_constant__ CUtensorMap tmap)
         auto emit_frame = [&]() {
             const uint32_t fnz = frm.nonzero();
             const int fa = frm.amax();
-            if (p.frames) {
+            if (!kNoFrames && p.frames) {
                 ga_frame f;
                 f.sumsq = frm.sum;
                 f.rms = __dsqrt_rn(__ddiv_rn(frm.sum, static_cast<double>(frm.n)));
@@ -290,7 +291,7 @@ ingest_kernel(const IngestParams p, const __grid_constant__ CUtensorMap tmap)
         auto chain = [&](float x) {
             const double q = sq_f64(x);
             msg_sum += q;
-            frm.sum += q;
+            if (!kNoFrames) frm.sum += q;
         };
 
         for (uint32_t c = 0; c < c_nch; c++, it++) {
@@ -372,7 +373,7 @@ ingest_kernel(const IngestParams p, const __grid_constant__ CUtensorMap tmap)
                                 for (int i = 0; i < 32; i++) {
                                     const double q = static_cast<double>(sqf[i]);
                                     msg_sum += q;
-                                    frm.sum += q;
+                                    if (!kNoFrames) frm.sum += q;   // the second strictly ordered chain: only when frames are wanted
                                 }
                             }
                             if (kFeat) {
@@ -576,12 +577,12 @@ extern "C" int ga_k_ingest(const void *d_pcm, const ga_desc *d_desc, uint32_t n_
     // the cooperative coalesced store pass otherwise (HBM-bound).
     switch (mode) {
         case 1: return launch_ingest<128, 2, 1, 1>(p, none, st);
-        case 2: return launch_ingest<128, 2, 2, 1>(p, none, st);
-        case 3: return launch_ingest<128, 2, 3, 1>(p, none, st);
+        case 2: return p.frames ? launch_ingest<128, 2, 2, 1>(p, none, st) : launch_ingest<128, 2, 2, 1 | 8>(p, none, st);
+        case 3: return p.frames ? launch_ingest<128, 2, 3, 1>(p, none, st) : launch_ingest<128, 2, 3, 1 | 8>(p, none, st);
         case 4: return launch_ingest<128, 3, 4, 0>(p, none, st);
         case 5: return launch_ingest<128, 2, 5, 0>(p, none, st);
-        case 6: return launch_ingest<128, 2, 6, 0>(p, none, st);
-        default: return launch_ingest<128, 2, 7, 0>(p, none, st);
+        case 6: return p.frames ? launch_ingest<128, 2, 6, 0>(p, none, st) : launch_ingest<128, 2, 6, 0 | 8>(p, none, st);
+        default: return p.frames ? launch_ingest<128, 2, 7, 0>(p, none, st) : launch_ingest<128, 2, 7, 0 | 8>(p, none, st);
     }
 }
 
@@ -624,11 +625,11 @@ extern "C" int ga_k_ingest_uniform(const void *d_pcm, const ga_desc *d_desc, uin
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     switch (mode) {
         case 1: return launch_ingest<128, 2, 1, 5>(p, tmap, st);
-        case 2: return launch_ingest<128, 2, 2, 5>(p, tmap, st);
-        case 3: return launch_ingest<128, 2, 3, 5>(p, tmap, st);
+        case 2: return p.frames ? launch_ingest<128, 2, 2, 5>(p, tmap, st) : launch_ingest<128, 2, 2, 5 | 8>(p, tmap, st);
+        case 3: return p.frames ? launch_ingest<128, 2, 3, 5>(p, tmap, st) : launch_ingest<128, 2, 3, 5 | 8>(p, tmap, st);
         case 4: return launch_ingest<128, 3, 4, 4>(p, tmap, st);
         case 5: return launch_ingest<128, 2, 5, 4>(p, tmap, st);
-        case 6: return launch_ingest<128, 2, 6, 4>(p, tmap, st);
-        default: return launch_ingest<128, 2, 7, 4>(p, tmap, st);
+        case 6: return p.frames ? launch_ingest<128, 2, 6, 4>(p, tmap, st) : launch_ingest<128, 2, 6, 4 | 8>(p, tmap, st);
+        default: return p.frames ? launch_ingest<128, 2, 7, 4>(p, tmap, st) : launch_ingest<128, 2, 7, 4 | 8>(p, tmap, st);
     }
 }
