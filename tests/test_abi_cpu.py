@@ -94,3 +94,23 @@ def test_audio_hash_wire_format():
     assert format_audio_hash(bytes(range(224, 256))) == "sha256:" + bytes(range(224, 256)).hex()
     with pytest.raises(ValueError):
         format_audio_hash(b"short")
+
+
+def test_reference_arm_of_the_bench_never_loads_the_product_library():
+    """`bench.py --impl reference` times the reference's CPU path only: it must print the contract's
+    JSON line (same metric / unit / config as the GPU arm, a thread-scaling table) without mapping
+    libgpuaudio.so — its input comes from oracle/synth_oracle.c."""
+    import json
+    import subprocess
+    import sys
+    code = ("import sys, json; sys.argv = ['bench.py', '--impl', 'reference', '--workload', 'cfg2', '--steps', '1', "
+            "'--warmup', '0', '--cpu-threads', '2']; import bench; bench.main(); "
+            "sys.stderr.write('MAPS_HAVE_PRODUCT=%d\\n' % ('libgpuaudio' in open('/proc/self/maps').read()))")
+    r = subprocess.run([sys.executable, "-c", code], cwd=ROOT, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "MAPS_HAVE_PRODUCT=0" in r.stderr
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["unit"] == "audio-s/s" and line["higher_is_better"] is True
+    assert line["config"]["workload"].startswith("cfg2: configs[1]")
+    assert set(line["cpu_baseline"]["scaling"]) == {"1", "2"} and line["cpu_baseline"]["kind"] == "port"
+    assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["value"] > 0
