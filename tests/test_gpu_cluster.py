@@ -156,7 +156,8 @@ def test_hub_over_two_gpus_spanning_windows_and_winner_audio():
                         assert svc.on_chunk(name(g, r), pcm[g, r][m * ms:(m + 1) * ms].tobytes(), True, False, (10 * m + n_relays - 1 - r) * MS)
             assert svc.flush() == n_groups * n_relays * wake_msgs
             assert svc.poll(now_us=50 * MS) == 0
-            assert svc.poll(now_us=200 * MS) == n_groups
+            closed = svc.poll_windows(200 * MS)                              # ga_hub_poll that also names the windows it closed
+            assert len(closed) == n_groups
             for g in range(n_groups):
                 sig = [ora.bytes_to_float32(pcm[g, r][:wake_msgs * ms].tobytes())[0] for r in reversed(range(n_relays))]
                 w, sc, _ = ora.arbitrate(sig)
@@ -175,6 +176,13 @@ def test_hub_over_two_gpus_spanning_windows_and_winner_audio():
             for g in range(n_groups):
                 full = ora.bytes_to_float32(pcm[g, 0].tobytes())[0]
                 assert svc.fetch_wav(name(g, 0)) == ora.float32_to_wav(full, 16000)
+            # ... and all winners at once, one gather + hash + copy per GPU (winners sit on both GPUs)
+            import hashlib
+            for w, (wav, audio_hash) in zip(closed, svc.fetch_winner_wavs(closed)):
+                g = int(svc.window(w).winner_id[1:].split("-")[0])
+                full = ora.bytes_to_float32(pcm[g, 0].tobytes())[0]
+                assert wav == ora.float32_to_wav(full, 16000)
+                assert audio_hash == "sha256:" + hashlib.sha256(full.astype("<f4").tobytes()).hexdigest()
             svc.close()
     finally:
         for c in ctxs:
