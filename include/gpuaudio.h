@@ -327,7 +327,9 @@ typedef struct ga_config {
                                    another chunk of its stream in the SAME ga_submit needs that
                                    predecessor to hold at least 47 frames                    */
 
-/* audio_service.go:233-244 is where the hub would call this (createAudioService). */
+/* audio_service.go:233-244 is where the hub would call this (createAudioService).  Everything the
+ * real-time path needs is allocated here, and the window-close and winner-path kernels are launched
+ * once on an empty stream, so that no allocation or module load lands in the first window close. */
 int  ga_init(const ga_config *cfg, ga_ctx **out);
 void ga_shutdown(ga_ctx *ctx);
 const char *ga_last_error(void);
