@@ -63,6 +63,9 @@ __constant__ uint32_t c_tap_bits[kTaps] = GA_RESAMPLE_TAP_BITS;
 #ifndef GA_RS_ROLLCONV
 #define GA_RS_ROLLCONV 1
 #endif
+#ifndef GA_RS_EVICT_FIRST
+#define GA_RS_EVICT_FIRST 1
+#endif
 #ifndef GA_RS_FMA1
 #define GA_RS_FMA1 1
 #endif
@@ -146,6 +149,8 @@ resample48_kernel(const ResampleParams p)
     }
     __syncwarp();
 
+    // the PCM is read once: evict-first in L2, so that the outputs pass 2 comes back for stay there
+    const uint64_t pcm_policy = l2_policy_evict_first();
     const uint32_t n_groups = (p.n_msgs + 31) / 32;
     uint32_t job = 0;                                           // messages staged so far by this warp
     for (uint32_t grp = blockIdx.x * kRsWarps + warp; grp < n_groups; grp += gridDim.x * kRsWarps) {
@@ -167,7 +172,11 @@ resample48_kernel(const ResampleParams p)
             if (lane == 0) {
                 const uint32_t bytes = (min(nb, static_cast<uint32_t>(kRsMaxFrames * 4)) + 15u) & ~15u;
                 mbar_arrive_expect_tx(&bars[j & 1], bytes);
+#if GA_RS_EVICT_FIRST
+                if (bytes) bulk_g2s_hint(wbase + (j & 1) * kPcmStage, p.pcm + in_off, bytes, &bars[j & 1], pcm_policy);
+#else
                 if (bytes) bulk_g2s(wbase + (j & 1) * kPcmStage, p.pcm + in_off, bytes, &bars[j & 1]);
+#endif
             }
         };
         issue(0, job);
